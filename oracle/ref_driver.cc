@@ -1,0 +1,250 @@
+/* ref_driver.cc -- C API around the UNMODIFIED reference blocks.
+ *
+ * Built by oracle/Makefile together with
+ *   /root/reference/lib/{cloud80211phy,signal_impl,signal2_impl,demod_impl,
+ *                        demod2_impl,decode_impl}.cc
+ * (compiled where they lie, against oracle/mockgr) into oracle/_ref/libref80211.so.
+ * Nothing here restates reference arithmetic: it only creates blocks through
+ * their public make() factories and plays scheduler (mock_scheduler.h).
+ * Test infrastructure / CPU baseline only -- never linked into the product.
+ */
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <gnuradio/block.h>
+#include <gnuradio/ieee80211/decode.h>
+#include <gnuradio/ieee80211/demod.h>
+#include <gnuradio/ieee80211/demod2.h>
+#include <gnuradio/ieee80211/signal.h>
+#include <gnuradio/ieee80211/signal2.h>
+#include "cloud80211phy.h"
+#include "mock_scheduler.h"
+
+using gr::mock_stream;
+
+struct ref_block {
+    std::shared_ptr<gr::block> blk;
+    std::vector<std::vector<uint8_t>> msgs;
+};
+
+static std::string g_key_tmp;
+
+extern "C" {
+
+/* ------------------------------------------------------------ streams */
+mock_stream* ref_stream_new(int itemsize, long nitems, const void* data)
+{
+    mock_stream* s = new mock_stream(itemsize);
+    if (nitems > 0) {
+        s->data.resize((size_t)nitems * itemsize);
+        if (data)
+            memcpy(s->data.data(), data, s->data.size());
+    }
+    return s;
+}
+void ref_stream_free(mock_stream* s) { delete s; }
+long ref_stream_nitems(const mock_stream* s) { return (long)s->nitems(); }
+int ref_stream_itemsize(const mock_stream* s) { return s->itemsize; }
+const void* ref_stream_data(const mock_stream* s) { return s->data.data(); }
+
+static void add_tag(mock_stream* s, long offset, const char* key, pmt::pmt_t v)
+{
+    gr::tag_t t;
+    t.offset = (uint64_t)offset;
+    t.key = pmt::mp(key);
+    t.value = v;
+    s->tags.push_back(t);
+}
+void ref_stream_add_tag_long(mock_stream* s, long offset, const char* key, long v)
+{
+    add_tag(s, offset, key, pmt::from_long(v));
+}
+void ref_stream_add_tag_float(mock_stream* s, long offset, const char* key, float v)
+{
+    add_tag(s, offset, key, pmt::from_float(v));
+}
+void ref_stream_add_tag_c32(mock_stream* s, long offset, const char* key, const float* data, int n)
+{
+    add_tag(s, offset, key, pmt::init_c32vector((size_t)n, reinterpret_cast<const std::complex<float>*>(data)));
+}
+int ref_stream_ntags(const mock_stream* s) { return (int)s->tags.size(); }
+long ref_stream_tag_offset(const mock_stream* s, int i) { return (long)s->tags[i].offset; }
+const char* ref_stream_tag_key(const mock_stream* s, int i)
+{
+    g_key_tmp = pmt::symbol_to_string(s->tags[i].key);
+    return g_key_tmp.c_str();
+}
+/* 0 long, 1 double, 2 c32 vector, -1 other */
+int ref_stream_tag_kind(const mock_stream* s, int i)
+{
+    switch (s->tags[i].value->kind) {
+    case pmt::K_LONG: return 0;
+    case pmt::K_DOUBLE: return 1;
+    case pmt::K_C32VEC: return 2;
+    default: return -1;
+    }
+}
+long ref_stream_tag_long(const mock_stream* s, int i) { return s->tags[i].value->l; }
+double ref_stream_tag_double(const mock_stream* s, int i) { return s->tags[i].value->d; }
+int ref_stream_tag_c32(const mock_stream* s, int i, float* out, int maxn)
+{
+    const auto& v = s->tags[i].value->c32;
+    int n = (int)std::min<size_t>(v.size(), (size_t)maxn);
+    if (out && n > 0) memcpy(out, v.data(), (size_t)n * 8);
+    return (int)v.size();
+}
+
+/* ------------------------------------------------------------- blocks */
+ref_block* ref_block_new(const char* kind, int a0, int a1)
+{
+    ref_block* b = new ref_block;
+    std::string k(kind);
+    if (k == "signal")
+        b->blk = gr::ieee80211::signal::make();
+    else if (k == "signal2")
+        b->blk = gr::ieee80211::signal2::make();
+    else if (k == "demod")
+        b->blk = gr::ieee80211::demod::make(a0, a1);
+    else if (k == "demod2")
+        b->blk = gr::ieee80211::demod2::make();
+    else if (k == "decode")
+        b->blk = gr::ieee80211::decode::make(a0 != 0);
+    else {
+        delete b;
+        return nullptr;
+    }
+    return b;
+}
+void ref_block_free(ref_block* b) { delete b; }
+
+/* Run the block over whole streams; nout = 0 for a sink (decode).
+ * Returns the number of general_work calls, or -1 on an exception. */
+long ref_block_run(ref_block* b, mock_stream** ins, int nin, mock_stream** outs, int nout, long chunk_in, long chunk_out)
+{
+    std::vector<const mock_stream*> vin(ins, ins + nin);
+    std::vector<mock_stream*> vout;
+    for (int o = 0; o < nout; o++) vout.push_back(outs[o]);
+    long calls;
+    try {
+        calls = gr::mock_run(*b->blk, vin, vout, chunk_in, chunk_out);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "ref_block_run: exception: %s\n", e.what());
+        return -1;
+    }
+    for (auto& m : b->blk->mock_msgs) {
+        /* every message on this path is pmt::cons(dict, blob) */
+        pmt::pmt_t payload = pmt::cdr(m.second);
+        b->msgs.push_back(payload->blob);
+    }
+    b->blk->mock_msgs.clear();
+    return calls;
+}
+int ref_block_nmsgs(const ref_block* b) { return (int)b->msgs.size(); }
+int ref_block_msg_len(const ref_block* b, int i) { return (int)b->msgs[i].size(); }
+const uint8_t* ref_block_msg_data(const ref_block* b, int i) { return b->msgs[i].data(); }
+void ref_block_clear_msgs(ref_block* b) { b->msgs.clear(); }
+
+/* ------------------------------------------- PHY library entry points
+ * Thin pass-throughs to free functions of the reference's cloud80211phy.cc,
+ * for unit-level parity tests of the restatement and of the CUDA kernels. */
+void ref_fill_mod_legacy(int mcs, int len, c8p_mod* m) { signalParserL(mcs, len, m); }
+
+/* fields of c8p_mod that matter on the path, in a fixed order */
+static void mod_to_ints(const c8p_mod& m, int* o)
+{
+    o[0] = m.format; o[1] = m.sumu; o[2] = m.ampdu; o[3] = m.nSym; o[4] = m.nSymSamp;
+    o[5] = m.nSD; o[6] = m.nSS; o[7] = m.nLTF; o[8] = m.mcs; o[9] = m.len;
+    o[10] = m.mod; o[11] = m.cr; o[12] = m.nBPSCS; o[13] = m.nDBPS; o[14] = m.nCBPS; o[15] = m.nCBPSS;
+}
+void ref_parse_legacy(int mcs, int len, int* out16)
+{
+    c8p_mod m;
+    memset(&m, 0, sizeof(m));
+    signalParserL(mcs, len, &m);
+    mod_to_ints(m, out16);
+}
+int ref_parse_ht(const uint8_t* bits48, int* out16)
+{
+    c8p_mod m;
+    c8p_sigHt s;
+    memset(&m, 0, sizeof(m));
+    uint8_t b[48];
+    memcpy(b, bits48, 48);
+    if (!signalCheckHt(b)) return 0;
+    signalParserHt(b, &m, &s);
+    mod_to_ints(m, out16);
+    return 1;
+}
+int ref_parse_vht(const uint8_t* sigA48, const uint8_t* sigB26, int* out16)
+{
+    c8p_mod m;
+    c8p_sigVhtA s;
+    memset(&m, 0, sizeof(m));
+    uint8_t a[48], bb[26];
+    memcpy(a, sigA48, 48);
+    memcpy(bb, sigB26, 26);
+    if (!signalCheckVhtA(a)) return 0;
+    signalParserVhtA(a, &m, &s);
+    signalParserVhtB(bb, &m);
+    mod_to_ints(m, out16);
+    return 1;
+}
+void ref_qam_to_llr(int mod, int nSD, const float* qam_in, float* llr_out)
+{
+    c8p_mod m;
+    memset(&m, 0, sizeof(m));
+    m.mod = mod;
+    m.nSD = nSD;
+    std::vector<gr_complex> q(nSD);
+    memcpy(q.data(), qam_in, (size_t)nSD * 8);
+    procSymQamToLlr(q.data(), llr_out, &m);
+}
+/* which: 0 legacy, 1 non-legacy stream 1, 2 non-legacy stream 2 */
+void ref_deint(int which, int nCBPSS, const float* in, float* out)
+{
+    c8p_mod m;
+    memset(&m, 0, sizeof(m));
+    m.nCBPS = nCBPSS;
+    m.nCBPSS = nCBPSS;
+    std::vector<float> tmp(in, in + nCBPSS);
+    if (which == 0)
+        procSymDeintL2(tmp.data(), out, &m);
+    else if (which == 1)
+        procSymDeintNL2SS1(tmp.data(), out, &m);
+    else
+        procSymDeintNL2SS2(tmp.data(), out, &m);
+}
+void ref_depas2(int nBPSCS, int nCBPSS, const float* in0, const float* in1, float* out)
+{
+    static float in[C8P_MAX_N_SS][C8P_MAX_N_CBPSS];
+    c8p_mod m;
+    memset(&m, 0, sizeof(m));
+    m.nBPSCS = nBPSCS;
+    m.nCBPSS = nCBPSS;
+    memcpy(in[0], in0, (size_t)nCBPSS * 4);
+    memcpy(in[1], in1, (size_t)nCBPSS * 4);
+    procSymDepasNL(in, out, &m);
+}
+void ref_sv_decode(const float* llr, uint8_t* bits, int trellis)
+{
+    std::vector<float> tmp(llr, llr + 2 * (size_t)trellis);
+    SV_Decode_Sig(tmp.data(), bits, trellis);
+}
+void ref_bcc_encode(const uint8_t* in, uint8_t* out, int len)
+{
+    std::vector<uint8_t> tmp(in, in + len);
+    bccEncoder(tmp.data(), out, len);
+}
+void ref_sv_tables(int* next128, int* output128)
+{
+    for (int i = 0; i < 64; i++)
+        for (int b = 0; b < 2; b++) {
+            next128[2 * i + b] = SV_STATE_NEXT[i][b];
+            output128[2 * i + b] = SV_STATE_OUTPUT[i][b];
+        }
+}
+void ref_pilot_p(float* out127) { memcpy(out127, PILOT_P, sizeof(float) * 127); }
+
+} /* extern "C" */
