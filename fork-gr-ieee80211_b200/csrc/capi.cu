@@ -1,0 +1,688 @@
+/* capi.cu -- host side of libw80211rx.so: the C ABI of include/w80211rx.h.
+ *
+ * One ctx per GPU.  A ctx owns `nslots` independent slots (stream + events + device buffers +
+ * pinned staging); a slot runs one batch at a time:
+ *
+ *   H2D(IQ, packet table, legacy H)            [host memory input only]
+ *   header kernel   -> descriptors             hdr.cu
+ *   D2H(descriptors), host plan                LLR offsets, symbol prefix sums, packets sorted by
+ *                                              (code rate, trellis length) into groups of 32, output offsets
+ *   H2D(plan)
+ *   demod kernel    -> LLRs (stay in HBM)      demod.cu
+ *   viterbi kernel  -> survivor words          viterbi.cu
+ *   traceback kernel-> decoded bit words       viterbi.cu
+ *   post kernel     -> PSDU bytes, MPDU records, counters   post.cu
+ *   D2H(bytes, records, counters)
+ *
+ * The only host synchronisation inside a batch is the one after the header kernel; with two slots
+ * the GPU works on one batch while the host plans the other.
+ */
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+#include "common.cuh"
+
+extern "C" void w80211_fill_tables(W80211Tables* t);
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+enum { EV_START, EV_H2D, EV_HDR, EV_PLAN, EV_DEMOD, EV_VIT, EV_TB, EV_POST, EV_END, EV_COUNT };
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[EV_COUNT] = {};
+    bool busy = false;
+    /* device */
+    DevBuf iq[2], pkts, chan_in, desc, chan, symprefix, llr, surv, bits, bytes, mpdus, counters, slot_pkt, pkt_slot, grp,
+        dec_list, psdu_off;
+    /* pinned */
+    PinBuf h_desc, h_plan, h_mpdus, h_counters;
+    /* batch in flight */
+    int npkt = 0, nant = 1, ngroups = 0, ndec = 0, nsymtot = 0;
+    bool did_demod = false, did_decode = false, in_host = true;
+    uint64_t n_llr = 0, n_bytes = 0, trellis_steps = 0;
+    uint32_t mpdu_cap = 0;
+    uint32_t launches = 0;
+    w80211_batch_out* out = nullptr;
+    std::vector<uint32_t> h_psdu_off;
+    w80211_timing timing = {};
+};
+
+} // namespace
+
+struct w80211_ctx {
+    int device = 0;
+    int nslots = 2;
+    W80211Tables* d_tab = nullptr;
+    Slot slots[4];
+    w80211_stats stats = {};
+    std::string err;
+};
+
+namespace {
+
+int fail(w80211_ctx* c, int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                              \
+    do {                                                                                                      \
+        cudaError_t e_ = (call);                                                                              \
+        if (e_ != cudaSuccess) return fail(ctx, W80211_E_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+int dev_reserve(w80211_ctx* ctx, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return 0;
+    if (b.p) CK(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes + bytes / 8 + 4096;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        want = bytes;
+        e = cudaMalloc(&b.p, want);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, W80211_E_NOMEM, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+        }
+    }
+    b.cap = want;
+    return 0;
+}
+
+int pin_reserve(w80211_ctx* ctx, PinBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return 0;
+    if (b.p) CK(cudaFreeHost(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes + bytes / 4 + 4096;
+    CK(cudaHostAlloc(&b.p, want, cudaHostAllocDefault));
+    b.cap = want;
+    return 0;
+}
+
+#define RS(call)            \
+    do {                    \
+        int r_ = (call);    \
+        if (r_ < 0) return r_; \
+    } while (0)
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+/* LLRs one packet needs for `trellis` steps at code rate cr (depuncturing of decode_impl.cc:210-229) */
+inline long long llr_needed(int trellis, int cr)
+{
+    static const int per[4] = {1, 2, 3, 5}, cnt[4] = {2, 3, 4, 6};
+    long long full = trellis / per[cr], rem = trellis % per[cr];
+    long long n = full * cnt[cr];
+    /* phase 0 takes 2, every later phase 1 */
+    if (rem > 0) n += 2 + (rem - 1);
+    return n;
+}
+
+struct Plan {
+    std::vector<int> order;
+};
+
+/* Host plan after the header stage.  Fills llr offsets in h_desc, uploads the plan arrays. */
+int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, bool do_decode)
+{
+    const int npkt = s.npkt;
+    /* LLR layout and symbol prefix sums */
+    uint64_t off = 0;
+    std::vector<int> symprefix(npkt + 1, 0);
+    for (int p = 0; p < npkt; p++) {
+        w80211_desc& d = hd[p];
+        int nsym = 0;
+        if (d.status == W80211_ST_OK && d.total > 0) {
+            if (assign_llr) {
+                d.llr_off = (int64_t)off;
+                off += align_up((size_t)d.total, 4) + 16;
+            }
+            nsym = d.nsym;
+        } else if (assign_llr) {
+            d.llr_off = -1;
+        }
+        symprefix[p + 1] = symprefix[p] + nsym;
+    }
+    if (assign_llr) s.n_llr = off;
+    s.nsymtot = symprefix[npkt];
+
+    /* packets to decode, sorted by (code rate, trellis descending) */
+    std::vector<int> dec;
+    s.trellis_steps = 0;
+    if (do_decode) {
+        for (int p = 0; p < npkt; p++) {
+            const w80211_desc& d = hd[p];
+            if (d.status != W80211_ST_OK) continue;
+            /* decode_impl.cc:93: len > 4095 or trellis > 32782 -> skipped */
+            if (d.len > W80211_B_MAX || d.len < 0 || d.trellis > W80211_T_MAX || d.trellis <= 0) continue;
+            if (d.cr < 0 || d.cr > 3 || d.llr_off < 0 || (d.llr_off & 3)) continue;
+            if (llr_needed(d.trellis, d.cr) > (long long)d.total) continue;
+            dec.push_back(p);
+            s.trellis_steps += (uint64_t)d.trellis;
+        }
+        std::stable_sort(dec.begin(), dec.end(), [&](int a, int b) {
+            if (hd[a].cr != hd[b].cr) return hd[a].cr < hd[b].cr;
+            return hd[a].trellis > hd[b].trellis;
+        });
+    }
+    s.ndec = (int)dec.size();
+    std::vector<int> slot_pkt, pkt_slot(npkt, -1);
+    std::vector<int4> grp;
+    s.h_psdu_off.assign(npkt, 0);
+    uint64_t row = 0, wrow = 0, boff = 0;
+    for (size_t i = 0; i < dec.size();) {
+        int cr = hd[dec[i]].cr;
+        int maxT = hd[dec[i]].trellis;
+        int4 G;
+        G.x = (int)row;
+        G.y = (maxT + 1) & ~1;
+        G.z = (int)wrow;
+        G.w = cr;
+        int k = 0;
+        for (; k < 32 && i < dec.size() && hd[dec[i]].cr == cr; k++, i++) {
+            pkt_slot[dec[i]] = (int)slot_pkt.size();
+            slot_pkt.push_back(dec[i]);
+        }
+        for (; k < 32; k++) slot_pkt.push_back(-1);
+        grp.push_back(G);
+        row += (uint64_t)G.y;
+        wrow += (uint64_t)((maxT + 31) >> 5);
+        if (row > 0x7fffffffull) return fail(ctx, W80211_E_CAPACITY, "batch too large: survivor rows overflow");
+    }
+    for (int p : dec) {
+        s.h_psdu_off[p] = (uint32_t)boff;
+        boff += align_up((size_t)((hd[p].trellis - 16 + 7) / 8) + 8, 16);
+        if (boff > 0xffffffffull) return fail(ctx, W80211_E_CAPACITY, "batch too large: output bytes overflow 4 GiB");
+    }
+    s.n_bytes = boff;
+    s.ngroups = (int)grp.size();
+
+    /* device buffers */
+    RS(dev_reserve(ctx, s.symprefix, (size_t)(npkt + 1) * 4));
+    if (assign_llr) RS(dev_reserve(ctx, s.llr, (size_t)(s.n_llr + 64) * 4));
+    if (do_decode) {
+        RS(dev_reserve(ctx, s.surv, (size_t)row * 32 * 8 + 1024));
+        RS(dev_reserve(ctx, s.bits, (size_t)wrow * 32 * 4 + 1024));
+        RS(dev_reserve(ctx, s.bytes, (size_t)boff + 64));
+        RS(dev_reserve(ctx, s.slot_pkt, slot_pkt.size() * 4 + 4));
+        RS(dev_reserve(ctx, s.pkt_slot, (size_t)npkt * 4 + 4));
+        RS(dev_reserve(ctx, s.grp, grp.size() * 16 + 16));
+        RS(dev_reserve(ctx, s.dec_list, dec.size() * 4 + 4));
+        RS(dev_reserve(ctx, s.psdu_off, (size_t)npkt * 4 + 4));
+        RS(dev_reserve(ctx, s.counters, 64));
+    }
+    /* pinned staging for the plan, one block */
+    size_t sz_sym = (size_t)(npkt + 1) * 4, sz_sp = slot_pkt.size() * 4, sz_ps = (size_t)npkt * 4, sz_g = grp.size() * 16,
+           sz_d = dec.size() * 4, sz_po = (size_t)npkt * 4;
+    size_t o_sym = 0, o_sp = align_up(o_sym + sz_sym, 16), o_ps = align_up(o_sp + sz_sp, 16), o_g = align_up(o_ps + sz_ps, 16),
+           o_d = align_up(o_g + sz_g, 16), o_po = align_up(o_d + sz_d, 16), tot = align_up(o_po + sz_po, 16);
+    RS(pin_reserve(ctx, s.h_plan, tot));
+    char* hp = (char*)s.h_plan.p;
+    memcpy(hp + o_sym, symprefix.data(), sz_sym);
+    if (sz_sp) memcpy(hp + o_sp, slot_pkt.data(), sz_sp);
+    memcpy(hp + o_ps, pkt_slot.data(), sz_ps);
+    if (sz_g) memcpy(hp + o_g, grp.data(), sz_g);
+    if (sz_d) memcpy(hp + o_d, dec.data(), sz_d);
+    memcpy(hp + o_po, s.h_psdu_off.data(), sz_po);
+    cudaStream_t st = s.stream;
+    CK(cudaMemcpyAsync(s.symprefix.p, hp + o_sym, sz_sym, cudaMemcpyHostToDevice, st));
+    if (do_decode) {
+        if (sz_sp) CK(cudaMemcpyAsync(s.slot_pkt.p, hp + o_sp, sz_sp, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(s.pkt_slot.p, hp + o_ps, sz_ps, cudaMemcpyHostToDevice, st));
+        if (sz_g) CK(cudaMemcpyAsync(s.grp.p, hp + o_g, sz_g, cudaMemcpyHostToDevice, st));
+        if (sz_d) CK(cudaMemcpyAsync(s.dec_list.p, hp + o_d, sz_d, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(s.psdu_off.p, hp + o_po, sz_po, cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(s.counters.p, 0, 64, st));
+    }
+    /* descriptors with their LLR offsets back to the device */
+    CK(cudaMemcpyAsync(s.desc.p, hd, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyHostToDevice, st));
+    return 0;
+}
+
+int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
+{
+    cudaStream_t st = s.stream;
+    w80211_batch_out* out = s.out;
+    w_launch_viterbi(st, s.ngroups, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
+                     (const float*)s.llr.p, (uint2*)s.surv.p);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(s.ev[EV_VIT], st));
+    w_launch_traceback(st, s.ngroups, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
+                       (const uint2*)s.surv.p, (uint32_t*)s.bits.p);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(s.ev[EV_TB], st));
+    /* MPDU record capacity: one per packet is the rule; VHT A-MPDUs can hold more */
+    s.mpdu_cap = out->mpdus ? out->mpdu_capacity : 0;
+    uint32_t internal_cap = (uint32_t)std::max<size_t>((size_t)s.ndec * 2 + 64, s.mpdu_cap);
+    RS(dev_reserve(ctx, s.mpdus, (size_t)internal_cap * sizeof(w80211_mpdu)));
+    RS(pin_reserve(ctx, s.h_mpdus, (size_t)internal_cap * sizeof(w80211_mpdu)));
+    RS(pin_reserve(ctx, s.h_counters, 64));
+    s.mpdu_cap = internal_cap;
+    w_launch_post(st, s.ndec, (const int4*)s.grp.p, (const int*)s.pkt_slot.p, (const int*)s.dec_list.p,
+                  (const w80211_desc*)s.desc.p, (const uint32_t*)s.bits.p, (const uint32_t*)s.psdu_off.p, (uint8_t*)s.bytes.p,
+                  (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(s.ev[EV_POST], st));
+    if (s.ngroups > 0) s.launches += 3;
+    /* results */
+    CK(cudaMemcpyAsync(s.h_counters.p, s.counters.p, 64, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(s.h_mpdus.p, s.mpdus.p, (size_t)internal_cap * sizeof(w80211_mpdu), cudaMemcpyDeviceToHost, st));
+    if (out->bytes) {
+        if (out->bytes_capacity < s.n_bytes) return fail(ctx, W80211_E_CAPACITY, "bytes_capacity %llu < %llu needed",
+                                                         (unsigned long long)out->bytes_capacity, (unsigned long long)s.n_bytes);
+        if (s.n_bytes)
+            CK(cudaMemcpyAsync(out->bytes, s.bytes.p, s.n_bytes,
+                               out->mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+    }
+    if (out->psdu_off) {
+        if (out->mem == W80211_MEM_DEVICE)
+            CK(cudaMemcpyAsync(out->psdu_off, s.psdu_off.p, (size_t)s.npkt * 4, cudaMemcpyDeviceToDevice, st));
+        else
+            memcpy(out->psdu_off, s.h_psdu_off.data(), (size_t)s.npkt * 4);
+    }
+    return 0;
+}
+
+int finish_outputs(w80211_ctx* ctx, Slot& s)
+{
+    cudaStream_t st = s.stream;
+    w80211_batch_out* out = s.out;
+    const w80211_desc* hd = (const w80211_desc*)s.h_desc.p;
+    if (out->desc) {
+        if (out->mem == W80211_MEM_DEVICE)
+            CK(cudaMemcpyAsync(out->desc, s.desc.p, (size_t)s.npkt * sizeof(w80211_desc), cudaMemcpyDeviceToDevice, st));
+        else
+            memcpy(out->desc, hd, (size_t)s.npkt * sizeof(w80211_desc));
+    }
+    if (out->want_llr && out->llr) {
+        if (out->llr_capacity < s.n_llr) return fail(ctx, W80211_E_CAPACITY, "llr_capacity %llu < %llu needed",
+                                                     (unsigned long long)out->llr_capacity, (unsigned long long)s.n_llr);
+        if (s.n_llr)
+            CK(cudaMemcpyAsync(out->llr, s.llr.p, s.n_llr * 4,
+                               out->mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaEventRecord(s.ev[EV_END], st));
+    return 0;
+}
+
+/* front half shared by demod_batch and rx_submit */
+int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_batch_out* out, bool do_decode)
+{
+    if (!in || !out || in->npkt < 0 || (in->nant != 1 && in->nant != 2) || !in->iq[0] || (in->nant == 2 && !in->iq[1]) ||
+        (in->npkt > 0 && (!in->pkts || !in->chan)))
+        return fail(ctx, W80211_E_ARG, "bad batch_in");
+    if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy: collect it first");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = s.stream;
+    const int npkt = in->npkt;
+    s.npkt = npkt;
+    s.nant = in->nant;
+    s.out = out;
+    s.did_demod = true;
+    s.did_decode = do_decode;
+    s.launches = 0;
+    s.in_host = in->mem == W80211_MEM_HOST;
+    out->n_mpdu = out->n_crc_ok = 0;
+    out->n_bytes = out->n_llr = out->psdu_bits_ok = 0;
+    const int chan_stride = in->nant == 2 ? 520 : 64;
+    CK(cudaEventRecord(s.ev[EV_START], st));
+    const float2* d_iq[2] = {nullptr, nullptr};
+    const w80211_pkt_in* d_pk;
+    const float2* d_chin;
+    if (s.in_host) {
+        for (int a = 0; a < in->nant; a++) {
+            RS(dev_reserve(ctx, s.iq[a], (size_t)in->nsamples * 8 + 1024));
+            CK(cudaMemcpyAsync(s.iq[a].p, in->iq[a], (size_t)in->nsamples * 8, cudaMemcpyHostToDevice, st));
+            d_iq[a] = (const float2*)s.iq[a].p;
+        }
+        RS(dev_reserve(ctx, s.pkts, (size_t)npkt * sizeof(w80211_pkt_in) + 16));
+        RS(dev_reserve(ctx, s.chan_in, (size_t)npkt * 512 + 16));
+        if (npkt) {
+            CK(cudaMemcpyAsync(s.pkts.p, in->pkts, (size_t)npkt * sizeof(w80211_pkt_in), cudaMemcpyHostToDevice, st));
+            CK(cudaMemcpyAsync(s.chan_in.p, in->chan, (size_t)npkt * 512, cudaMemcpyHostToDevice, st));
+        }
+        d_pk = (const w80211_pkt_in*)s.pkts.p;
+        d_chin = (const float2*)s.chan_in.p;
+    } else {
+        for (int a = 0; a < in->nant; a++) d_iq[a] = (const float2*)in->iq[a];
+        d_pk = in->pkts;
+        d_chin = (const float2*)in->chan;
+    }
+    CK(cudaEventRecord(s.ev[EV_H2D], st));
+    RS(dev_reserve(ctx, s.desc, (size_t)npkt * sizeof(w80211_desc) + 16));
+    RS(dev_reserve(ctx, s.chan, (size_t)npkt * chan_stride * 8 + 16));
+    RS(pin_reserve(ctx, s.h_desc, (size_t)npkt * sizeof(w80211_desc) + 16));
+    w_launch_header(st, ctx->d_tab, npkt, in->nant, d_iq[0], d_iq[1], in->nsamples, d_pk, d_chin, (w80211_desc*)s.desc.p,
+                    (float2*)s.chan.p, chan_stride);
+    CK(cudaGetLastError());
+    if (npkt) s.launches += 1;
+    CK(cudaEventRecord(s.ev[EV_HDR], st));
+    if (npkt) CK(cudaMemcpyAsync(s.h_desc.p, s.desc.p, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    w80211_desc* hd = (w80211_desc*)s.h_desc.p;
+    RS(plan_and_upload(ctx, s, hd, true, do_decode));
+    CK(cudaEventRecord(s.ev[EV_PLAN], st));
+    w_launch_demod(st, ctx->d_tab, s.nsymtot, npkt, in->nant, d_iq[0], d_iq[1], d_pk, (const w80211_desc*)s.desc.p,
+                   (const int*)s.symprefix.p, (const float2*)s.chan.p, chan_stride, (float*)s.llr.p);
+    CK(cudaGetLastError());
+    if (s.nsymtot) s.launches += 1;
+    CK(cudaEventRecord(s.ev[EV_DEMOD], st));
+    return 0;
+}
+
+int collect_slot(w80211_ctx* ctx, Slot& s)
+{
+    if (!s.busy) return fail(ctx, W80211_E_STATE, "slot idle: nothing to collect");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(s.stream));
+    s.busy = false;
+    w80211_batch_out* out = s.out;
+    const w80211_desc* hd = (const w80211_desc*)s.h_desc.p;
+    out->n_llr = s.n_llr;
+    w80211_stats& S = ctx->stats;
+    S.packets_in += (uint64_t)s.npkt;
+    S.kernel_launches += s.launches;
+    if (s.did_demod) {
+        for (int p = 0; p < s.npkt; p++) {
+            switch (hd[p].status) {
+            case W80211_ST_DROP_GATE: S.dropped_gate++; break;
+            case W80211_ST_NDP: S.ndp++; break;
+            case W80211_ST_UNSUPPORTED: S.unsupported++; break;
+            case W80211_ST_BAD_INPUT: S.bad_input++; break;
+            default: break;
+            }
+        }
+    }
+    if (s.did_decode) {
+        const unsigned int* c = (const unsigned int*)s.h_counters.p;
+        uint32_t n = c[0];
+        if (n > s.mpdu_cap) return fail(ctx, W80211_E_CAPACITY, "MPDU records overflow: %u > %u", n, s.mpdu_cap);
+        w80211_mpdu* hm = (w80211_mpdu*)s.h_mpdus.p;
+        std::sort(hm, hm + n, [](const w80211_mpdu& a, const w80211_mpdu& b) {
+            return a.pkt != b.pkt ? a.pkt < b.pkt : a.off < b.off;
+        });
+        out->n_mpdu = n;
+        out->n_crc_ok = c[1];
+        out->psdu_bits_ok = (uint64_t)c[2] | ((uint64_t)c[3] << 32);
+        out->n_bytes = s.n_bytes;
+        S.packets_decoded += (uint64_t)s.ndec;
+        S.trellis_steps += s.trellis_steps;
+        S.mpdu_total += n;
+        S.mpdu_crc_ok += c[1];
+        for (uint32_t i = 0; i < n; i++) {
+            if (!hm[i].crc_ok) continue;
+            const w80211_desc& d = hd[hm[i].pkt];
+            if (d.format == W80211_F_L && d.mcs >= 0 && d.mcs < 8) S.ok_legacy[d.mcs]++;
+            if (d.format == W80211_F_HT && d.mcs >= 0) S.ok_ht[d.mcs % 8]++;
+            if (d.format == W80211_F_VHT && d.mcs >= 0 && d.mcs < 10) S.ok_vht[d.mcs]++;
+        }
+        if (out->mpdus) {
+            if (out->mpdu_capacity < n) return fail(ctx, W80211_E_CAPACITY, "mpdu_capacity %u < %u", out->mpdu_capacity, n);
+            if (out->mem == W80211_MEM_DEVICE) {
+                CK(cudaMemcpy(out->mpdus, hm, (size_t)n * sizeof(w80211_mpdu), cudaMemcpyHostToDevice));
+            } else {
+                memcpy(out->mpdus, hm, (size_t)n * sizeof(w80211_mpdu));
+            }
+        }
+    }
+    /* stage timing */
+    auto ms = [&](int a, int b) {
+        float v = 0.f;
+        cudaEventElapsedTime(&v, s.ev[a], s.ev[b]);
+        return v;
+    };
+    w80211_timing& t = s.timing;
+    memset(&t, 0, sizeof(t));
+    if (s.did_demod) {
+        t.h2d = ms(EV_START, EV_H2D);
+        t.header = ms(EV_H2D, EV_HDR);
+        t.demod = ms(EV_PLAN, EV_DEMOD);
+    }
+    if (s.did_decode) {
+        t.viterbi = ms(s.did_demod ? EV_DEMOD : EV_PLAN, EV_VIT);
+        t.traceback = ms(EV_VIT, EV_TB);
+        t.post = ms(EV_TB, EV_POST);
+        t.d2h = ms(EV_POST, EV_END);
+    }
+    t.total = ms(EV_START, EV_END);
+    t.launches = s.launches;
+    cudaGetLastError();
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+int w80211_abi_version(void) { return W80211_ABI_VERSION; }
+
+int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
+{
+    if (!outp) return W80211_E_ARG;
+    *outp = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return W80211_E_CUDA; /* no CPU fallback */
+    }
+    w80211_ctx* ctx = new (std::nothrow) w80211_ctx();
+    if (!ctx) return W80211_E_NOMEM;
+    ctx->device = cfg ? cfg->device : 0;
+    ctx->nslots = cfg && cfg->nslots > 0 ? std::min(cfg->nslots, 4) : 2;
+    if (ctx->device < 0 || ctx->device >= ndev || cudaSetDevice(ctx->device) != cudaSuccess) {
+        delete ctx;
+        return W80211_E_ARG;
+    }
+    W80211Tables* ht = new W80211Tables;
+    w80211_fill_tables(ht);
+    bool ok = cudaMalloc(&ctx->d_tab, sizeof(W80211Tables)) == cudaSuccess &&
+              cudaMemcpy(ctx->d_tab, ht, sizeof(W80211Tables), cudaMemcpyHostToDevice) == cudaSuccess;
+    delete ht;
+    for (int i = 0; ok && i < ctx->nslots; i++) {
+        ok = cudaStreamCreateWithFlags(&ctx->slots[i].stream, cudaStreamNonBlocking) == cudaSuccess;
+        for (int e = 0; ok && e < EV_COUNT; e++) ok = cudaEventCreate(&ctx->slots[i].ev[e]) == cudaSuccess;
+    }
+    if (!ok) {
+        cudaGetLastError();
+        w80211_destroy(ctx);
+        return W80211_E_CUDA;
+    }
+    *outp = ctx;
+    return W80211_OK;
+}
+
+void w80211_destroy(w80211_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    for (int i = 0; i < 4; i++) {
+        Slot& s = ctx->slots[i];
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        DevBuf* db[] = {&s.iq[0], &s.iq[1], &s.pkts, &s.chan_in, &s.desc, &s.chan, &s.symprefix, &s.llr, &s.surv, &s.bits,
+                        &s.bytes, &s.mpdus, &s.counters, &s.slot_pkt, &s.pkt_slot, &s.grp, &s.dec_list, &s.psdu_off};
+        for (DevBuf* b : db)
+            if (b->p) cudaFree(b->p);
+        PinBuf* pb[] = {&s.h_desc, &s.h_plan, &s.h_mpdus, &s.h_counters};
+        for (PinBuf* b : pb)
+            if (b->p) cudaFreeHost(b->p);
+        for (int e = 0; e < EV_COUNT; e++)
+            if (s.ev[e]) cudaEventDestroy(s.ev[e]);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    if (ctx->d_tab) cudaFree(ctx->d_tab);
+    delete ctx;
+}
+
+const char* w80211_last_error(const w80211_ctx* ctx) { return ctx ? ctx->err.c_str() : "no context (CUDA device missing?)"; }
+
+int w80211_stats_get(const w80211_ctx* ctx, w80211_stats* out)
+{
+    if (!ctx || !out) return W80211_E_ARG;
+    *out = ctx->stats;
+    return 0;
+}
+
+int w80211_timing_get(const w80211_ctx* ctx, int slot, w80211_timing* out)
+{
+    if (!ctx || !out || slot < 0 || slot >= ctx->nslots) return W80211_E_ARG;
+    *out = ctx->slots[slot].timing;
+    return 0;
+}
+
+void* w80211_stream(const w80211_ctx* ctx, int slot)
+{
+    if (!ctx || slot < 0 || slot >= ctx->nslots) return nullptr;
+    return (void*)ctx->slots[slot].stream;
+}
+
+int w80211_rx_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w80211_batch_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
+    Slot& s = ctx->slots[slot];
+    RS(enqueue_front(ctx, s, in, out, true));
+    s.busy = true;
+    int r = enqueue_decode_tail(ctx, s);
+    if (r == 0) r = finish_outputs(ctx, s);
+    if (r < 0) {
+        cudaStreamSynchronize(s.stream);
+        s.busy = false;
+    }
+    return r;
+}
+
+int w80211_rx_collect(w80211_ctx* ctx, int slot)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
+    return collect_slot(ctx, ctx->slots[slot]);
+}
+
+int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out)
+{
+    int r = w80211_rx_submit(ctx, 0, in, out);
+    if (r < 0) return r;
+    return w80211_rx_collect(ctx, 0);
+}
+
+int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    Slot& s = ctx->slots[0];
+    RS(enqueue_front(ctx, s, in, out, false));
+    s.busy = true;
+    int r = finish_outputs(ctx, s);
+    if (r < 0) {
+        cudaStreamSynchronize(s.stream);
+        s.busy = false;
+        return r;
+    }
+    return collect_slot(ctx, s);
+}
+
+int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, const float* llr, uint64_t nllr,
+                        int32_t llr_mem, w80211_batch_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (npkt < 0 || !out || (npkt > 0 && (!desc || !llr))) return fail(ctx, W80211_E_ARG, "bad decode_batch arguments");
+    Slot& s = ctx->slots[0];
+    if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = s.stream;
+    s.npkt = npkt;
+    s.out = out;
+    s.did_demod = false;
+    s.did_decode = true;
+    s.launches = 0;
+    out->n_mpdu = out->n_crc_ok = 0;
+    out->n_bytes = out->n_llr = out->psdu_bits_ok = 0;
+    CK(cudaEventRecord(s.ev[EV_START], st));
+    RS(pin_reserve(ctx, s.h_desc, (size_t)npkt * sizeof(w80211_desc) + 16));
+    RS(dev_reserve(ctx, s.desc, (size_t)npkt * sizeof(w80211_desc) + 16));
+    w80211_desc* hd = (w80211_desc*)s.h_desc.p;
+    if (llr_mem == W80211_MEM_DEVICE) {
+        if (npkt) CK(cudaMemcpy(hd, desc, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost));
+    } else if (npkt) {
+        memcpy(hd, desc, (size_t)npkt * sizeof(w80211_desc));
+    }
+    /* LLRs into the slot's buffer at 16-byte aligned offsets */
+    uint64_t off = 0;
+    std::vector<uint64_t> src_off(npkt);
+    for (int p = 0; p < npkt; p++) {
+        w80211_desc& d = hd[p];
+        src_off[p] = (uint64_t)d.llr_off;
+        if (d.status == W80211_ST_OK && d.total > 0 && d.llr_off >= 0 && (uint64_t)d.llr_off + (uint64_t)d.total <= nllr) {
+            d.llr_off = (int64_t)off;
+            off += align_up((size_t)d.total, 4) + 16;
+        } else {
+            if (d.status == W80211_ST_OK) d.status = W80211_ST_BAD_INPUT;
+            d.llr_off = -1;
+        }
+    }
+    s.n_llr = off;
+    RS(dev_reserve(ctx, s.llr, (size_t)(off + 64) * 4));
+    for (int p = 0; p < npkt; p++) {
+        const w80211_desc& d = hd[p];
+        if (d.llr_off < 0) continue;
+        CK(cudaMemcpyAsync((float*)s.llr.p + d.llr_off, llr + src_off[p], (size_t)d.total * 4,
+                           llr_mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    }
+    CK(cudaEventRecord(s.ev[EV_H2D], st));
+    CK(cudaEventRecord(s.ev[EV_HDR], st));
+    int r = plan_and_upload(ctx, s, hd, false, true);
+    if (r < 0) return r;
+    CK(cudaEventRecord(s.ev[EV_PLAN], st));
+    CK(cudaEventRecord(s.ev[EV_DEMOD], st));
+    s.busy = true;
+    r = enqueue_decode_tail(ctx, s);
+    if (r == 0) {
+        /* hand back descriptors with the caller's own LLR offsets */
+        bool want = out->want_llr;
+        out->want_llr = 0;
+        w80211_desc* user_desc = out->desc;
+        out->desc = nullptr;
+        r = finish_outputs(ctx, s);
+        out->want_llr = want;
+        out->desc = user_desc;
+    }
+    if (r < 0) {
+        cudaStreamSynchronize(s.stream);
+        s.busy = false;
+        return r;
+    }
+    r = collect_slot(ctx, s);
+    if (r == 0 && out->desc && out->mem == W80211_MEM_HOST) {
+        for (int p = 0; p < npkt; p++) {
+            out->desc[p] = hd[p];
+            out->desc[p].llr_off = (int64_t)src_off[p];
+        }
+    }
+    return r;
+}
+
+} /* extern "C" */

@@ -1,0 +1,150 @@
+/* common.cuh -- shared device helpers of libw80211rx.
+ *
+ * Arithmetic policy.  Everything that feeds a decision (LLRs, path metrics) is
+ * computed as an explicit sequence of IEEE-754 operations that mirrors what
+ * the reference's C++ compiles to on x86-64 (no FMA contraction there):
+ *   complex * complex  -> (ac - bd, ad + bc), four binary32 products, rounded one by one
+ *                         (what g++ emits for std::complex<float>::operator*)
+ *   complex / complex  -> libgcc __divsc3 (GCC >= 12): products, sums and the two
+ *                         divisions in binary64, then rounded to binary32
+ *   std::abs(complex)  -> glibc hypotf: (float)sqrt((double)x*x + (double)y*y)
+ * so the CUDA path reproduces the oracle's floats bit for bit, not just within
+ * the 1e-4 tolerance the spec allows.  The library is built with -fmad=false and
+ * the helpers below use the _rn intrinsics anyway.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/w80211rx.h"
+#include "fft64_canon.h"
+
+#define W_WARP 32
+#define W_NMAPS 19
+#define W_MAPLEN 416
+
+/* Constant tables, generated on the host from the 802.11 formulas (tables.cc)
+ * and kept in device global memory. */
+struct W80211Tables {
+    float pilot_p[128];        /* p_0..p_126 pilot polarity (802.11-2016 17.3.5.10); reference PILOT_P cloud80211phy.cc:160-168 */
+    float ltf_nl[64];          /* HT/VHT-LTF sign per FFT bin, 0 on unused bins; reference LTF_NL_28_F_FLOAT :113-129 */
+    int8_t sig_demap[64];      /* FFT bin -> coded-bit index of a 48-bit BPSK SIG symbol, -1 unused; reference FFT_NL_SIG_DEMAP :31 */
+    int8_t bin_j_l[64];        /* FFT bin -> data subcarrier index (ascending frequency), legacy 48; -1 = null/pilot */
+    int8_t bin_j_nl[64];       /* same, HT/VHT 52 */
+    uint8_t sigb_deint[52];    /* reference mapDeintVhtSigB20 :1503 */
+    uint8_t sigb_int[52];      /* reference mapIntelVhtSigB20 :1508 */
+    /* interleaved LLR index -> index inside the symbol's nCBPS output block.
+     * 0..3 legacy nbpscs 1,2,4,6; 4..8 HT/VHT one stream nbpscs 1,2,4,6,8;
+     * 9..13 two streams, stream 1 (deinterleave + stream de-parse); 14..18 stream 2. */
+    uint16_t map[W_NMAPS][W_MAPLEN];
+};
+
+struct cf32 {
+    float x, y;
+};
+
+__device__ __forceinline__ cf32 c_make(float x, float y)
+{
+    cf32 r;
+    r.x = x;
+    r.y = y;
+    return r;
+}
+__device__ __forceinline__ cf32 c_add(cf32 a, cf32 b) { return c_make(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
+__device__ __forceinline__ cf32 c_sub(cf32 a, cf32 b) { return c_make(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y)); }
+__device__ __forceinline__ cf32 c_conj(cf32 a) { return c_make(a.x, -a.y); }
+__device__ __forceinline__ cf32 c_neg(cf32 a) { return c_make(-a.x, -a.y); }
+__device__ __forceinline__ cf32 c_scale(cf32 a, float f) { return c_make(__fmul_rn(a.x, f), __fmul_rn(a.y, f)); }
+__device__ __forceinline__ cf32 c_divf(cf32 a, float f) { return c_make(__fdiv_rn(a.x, f), __fdiv_rn(a.y, f)); }
+__device__ __forceinline__ cf32 c_mul(cf32 a, cf32 b)
+{
+    float ac = __fmul_rn(a.x, b.x), bd = __fmul_rn(a.y, b.y);
+    float ad = __fmul_rn(a.x, b.y), bc = __fmul_rn(a.y, b.x);
+    return c_make(__fsub_rn(ac, bd), __fadd_rn(ad, bc));
+}
+/* (a+ib)/(c+id) as libgcc's __divsc3 does it when binary64 hardware exists. */
+__device__ __forceinline__ cf32 c_div(cf32 n, cf32 d)
+{
+    double a = n.x, b = n.y, c = d.x, dd = d.y;
+    double denom = __dadd_rn(__dmul_rn(c, c), __dmul_rn(dd, dd));
+    double x = __ddiv_rn(__dadd_rn(__dmul_rn(a, c), __dmul_rn(b, dd)), denom);
+    double y = __ddiv_rn(__dsub_rn(__dmul_rn(b, c), __dmul_rn(a, dd)), denom);
+    return c_make(__double2float_rn(x), __double2float_rn(y));
+}
+/* std::abs(std::complex<float>) = hypotf */
+__device__ __forceinline__ float c_abs(cf32 a)
+{
+    double x = a.x, y = a.y;
+    return __double2float_rn(__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y))));
+}
+
+/* ---- 64-point FFT on 8 lanes (fft64_canon.h, n = 8*n1 + n2, k = k1 + 8*k2).
+ * Lane g (0..7 inside its 8-lane group) loads x[8*n1+g], runs the column FFT,
+ * twiddles, exchanges through shared memory and runs the row FFT.  On return
+ * lane g holds X[g + 8*k2] in (re[k2], im[k2]).  xch: 8 rows of 9 float2 per
+ * group (the pad keeps the 64-bit accesses conflict free). */
+#define W_FFT_XCH_FLOAT2 72
+/* per-lane twiddles W64^(g*k1), k1 = 1..7, read once per thread */
+__device__ __forceinline__ void fft64_twiddles(int g, float* wr, float* wi)
+{
+#pragma unroll
+    for (int k1 = 0; k1 < 8; k1++) {
+        wr[k1] = C8_W64_RE[(g * k1) & 63];
+        wi[k1] = C8_W64_IM[(g * k1) & 63];
+    }
+}
+__device__ __forceinline__ void fft64_lane8(const float2* __restrict__ src, int g, float2* xch, float* re, float* im,
+                                            const float* wr, const float* wi, bool valid)
+{
+#pragma unroll
+    for (int n1 = 0; n1 < 8; n1++) {
+        float2 v = valid ? __ldg(&src[8 * n1 + g]) : make_float2(0.f, 0.f);
+        re[n1] = v.x;
+        im[n1] = v.y;
+    }
+    c8_fft8(re, im);
+    if (g) { /* n2*k1 == 0 is left untouched, as in c8_fft64() */
+#pragma unroll
+        for (int k1 = 1; k1 < 8; k1++) {
+            float ar = re[k1], ai = im[k1];
+            re[k1] = C8_SUB(C8_MUL(ar, wr[k1]), C8_MUL(ai, wi[k1]));
+            im[k1] = C8_ADD(C8_MUL(ar, wi[k1]), C8_MUL(ai, wr[k1]));
+        }
+    }
+#pragma unroll
+    for (int k1 = 0; k1 < 8; k1++) xch[g * 9 + k1] = make_float2(re[k1], im[k1]);
+    __syncwarp();
+#pragma unroll
+    for (int n2 = 0; n2 < 8; n2++) {
+        float2 v = xch[n2 * 9 + g];
+        re[n2] = v.x;
+        im[n2] = v.y;
+    }
+    __syncwarp();
+    c8_fft8(re, im);
+}
+
+/* K=7 code of 802.11 (generators 133, 171 octal): 2-bit label A<<1|B of the branch that
+ * leaves state `st` (newest bit in bit 5) with input bit b.  Equals the reference's
+ * SV_STATE_OUTPUT[st][b] (cloud80211phy.cc:1877-1887); checked in tests/test_tables.py. */
+__host__ __device__ constexpr int w_branch_label(int st, int b)
+{
+    int x1 = (st >> 5) & 1, x2 = (st >> 4) & 1, x3 = (st >> 3) & 1, x5 = (st >> 1) & 1, x6 = st & 1;
+    int A = b ^ x2 ^ x3 ^ x5 ^ x6;
+    int B = b ^ x1 ^ x2 ^ x3 ^ x6;
+    return (A << 1) | B;
+}
+
+/* kernels (one translation unit each) */
+void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nant, const float2* iq0, const float2* iq1,
+                     unsigned long long nsamples, const w80211_pkt_in* pk, const float2* chan_in, w80211_desc* desc,
+                     float2* chan_out, int chan_stride);
+void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nsymtot, int npkt, int nant, const float2* iq0,
+                    const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* sym_prefix,
+                    const float2* chan, int chan_stride, float* llr);
+void w_launch_viterbi(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
+                      const float* llr, uint2* surv);
+void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
+                        const uint2* surv, uint32_t* bits);
+void w_launch_post(cudaStream_t st, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,
+                   const w80211_desc* desc, const uint32_t* bits, const uint32_t* psdu_off, uint8_t* out_bytes,
+                   w80211_mpdu* mpdus, unsigned int mpdu_cap, unsigned int* counters);

@@ -1,0 +1,212 @@
+/* post.cu -- descramble, byte packing, A-MPDU walk and FCS, one warp per decoded packet.
+ *
+ * Replaces decode_impl::descramble (lib/decode_impl.cc:304-323) and decode_impl::packetAssemble
+ * (:325-520) including the boost::crc_32_type check (decode_impl.h:84, :372-374, :451-453).
+ *
+ *  - descramble: the 7-bit scrambler state is read from the first 7 decoded bits; the x^7+x^4+1
+ *    sequence is generated once per packet (160 bits) and applied 32 bits at a time;
+ *  - bytes: LSB first from bit 16, i.e. the descrambled bit words viewed as bytes, offset 2;
+ *  - CRC-32 (reflected 0xEDB88320, init/xorout 0xFFFFFFFF): every lane runs a table CRC over its
+ *    own slice of the MPDU, the 32 partial CRCs are merged with x^(8n) multiplications in
+ *    GF(2)[x]/P, and the result is compared with the residue 558161692 the reference tests for;
+ *  - VHT: the delimiter walk of the reference, with its quirks (no delimiter CRC/signature check,
+ *    length bits OR-ed into a value that survives from the previous subframe, +4 after a pass).
+ */
+#include "common.cuh"
+
+#define POST_WARPS 4
+#define POST_MAXW 1028 /* ceil(32782/32) = 1025 words, padded */
+#define CRC_POLY 0xEDB88320u
+#define CRC_RESIDUE 558161692u
+
+struct PostSmem {
+    uint32_t crc_tab[256];
+    uint32_t x2n[32]; /* x^(2^k) mod P, reflected */
+    uint32_t dw[POST_WARPS][POST_MAXW];
+    uint32_t seq[POST_WARPS][8];
+};
+
+/* a(x) * b(x) mod P, reflected bit order (bit 31 = x^0) */
+__device__ __forceinline__ uint32_t gf_mul(uint32_t a, uint32_t b)
+{
+    uint32_t p = 0;
+#pragma unroll 4
+    for (int i = 31; i >= 0; i--) {
+        if ((a >> i) & 1u) p ^= b;
+        b = (b & 1u) ? (b >> 1) ^ CRC_POLY : (b >> 1);
+    }
+    return p;
+}
+
+/* x^(8*nbytes) mod P */
+__device__ __forceinline__ uint32_t x_pow_bytes(const uint32_t* x2n, uint32_t nbytes)
+{
+    uint32_t p = 0x80000000u; /* x^0 */
+    int k = 3;
+    while (nbytes) {
+        if (nbytes & 1u) p = gf_mul(x2n[k & 31], p);
+        nbytes >>= 1;
+        k++;
+    }
+    return p;
+}
+
+/* standard CRC-32 of by[0..n), computed by the whole warp; every lane gets the result */
+__device__ uint32_t warp_crc32(const PostSmem& S, const uint8_t* by, int n, int lane)
+{
+    if (n <= 0) return 0u;
+    int c = (n + 31) >> 5;
+    c = (c + 3) & ~3;
+    if (!((c >> 2) & 1)) c += 4; /* odd number of words per lane: conflict-free shared reads */
+    int beg = lane * c, end = min(n, beg + c);
+    uint32_t crc = 0u;
+    if (beg < end) {
+        crc = 0xFFFFFFFFu;
+        for (int k = beg; k < end; k++) crc = S.crc_tab[(crc ^ by[k]) & 0xffu] ^ (crc >> 8);
+        crc ^= 0xFFFFFFFFu;
+        int after = n - end;
+        if (after > 0) crc = gf_mul(x_pow_bytes(S.x2n, (uint32_t)after), crc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) crc ^= __shfl_xor_sync(0xffffffffu, crc, o);
+    return crc;
+}
+
+__device__ __forceinline__ void emit(int lane, uint32_t pkt, uint32_t off, uint32_t len, bool ok, w80211_mpdu* mpdus,
+                                     unsigned int cap, unsigned int* counters)
+{
+    if (lane == 0) {
+        unsigned int idx = atomicAdd(&counters[0], 1u);
+        if (idx < cap) {
+            w80211_mpdu r;
+            r.pkt = pkt;
+            r.off = off;
+            r.len = len;
+            r.crc_ok = ok ? 1u : 0u;
+            mpdus[idx] = r;
+        }
+        if (ok) {
+            atomicAdd(&counters[1], 1u);
+            atomicAdd(reinterpret_cast<unsigned long long*>(&counters[2]), (unsigned long long)len * 8ull);
+        }
+    }
+}
+
+/* counters: [0] MPDU records, [1] FCS-valid MPDUs, [2..3] 64-bit sum of 8*len over FCS-valid MPDUs */
+__global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(int ndec, const int4* __restrict__ grp, const int* __restrict__ pkt_slot,
+                                                               const int* __restrict__ dec_list, const w80211_desc* __restrict__ desc,
+                                                               const uint32_t* __restrict__ bits, const uint32_t* __restrict__ psdu_off,
+                                                               uint8_t* __restrict__ out_bytes, w80211_mpdu* __restrict__ mpdus,
+                                                               unsigned int mpdu_cap, unsigned int* __restrict__ counters)
+{
+    __shared__ PostSmem S;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    for (int i = tid; i < 256; i += blockDim.x) {
+        uint32_t c = (uint32_t)i;
+        for (int k = 0; k < 8; k++) c = (c & 1u) ? (CRC_POLY ^ (c >> 1)) : (c >> 1);
+        S.crc_tab[i] = c;
+    }
+    if (tid == 0) {
+        uint32_t p = 0x40000000u; /* x^1 */
+        S.x2n[0] = p;
+        for (int k = 1; k < 32; k++) {
+            p = gf_mul(p, p);
+            S.x2n[k] = p;
+        }
+    }
+    __syncthreads();
+    const int q = blockIdx.x * POST_WARPS + wid;
+    if (q >= ndec) return;
+    const int pkt = dec_list[q];
+    const int slot = pkt_slot[pkt];
+    const int4 G = grp[slot >> 5];
+    const w80211_desc d = desc[pkt];
+    const int T = d.trellis;
+    const int nw = (T + 31) >> 5;
+    const uint32_t* src = bits + (size_t)G.z * 32 + (slot & 31);
+    uint32_t* dw = S.dw[wid];
+
+    /* scrambler state from the first 7 bits (decode_impl.cc:308-314), then 160 sequence bits */
+    uint32_t w0 = __ldg(src);
+    if (lane == 0) {
+        int state = 0;
+        for (int i = 0; i < 7; i++)
+            if ((w0 >> i) & 1u) state |= 1 << (6 - i);
+        uint32_t acc = 0;
+        for (int k = 0; k < 160; k++) {
+            int fb = ((state >> 6) & 1) ^ ((state >> 3) & 1);
+            state = ((state << 1) & 0x7e) | fb;
+            acc |= (uint32_t)fb << (k & 31);
+            if ((k & 31) == 31) {
+                S.seq[wid][k >> 5] = acc;
+                acc = 0;
+            }
+        }
+        S.seq[wid][5] = 0;
+    }
+    __syncwarp();
+    const uint32_t* seq = S.seq[wid];
+    for (int j = lane; j < nw + 1; j += 32) {
+        uint32_t v = 0;
+        if (j < nw) {
+            uint32_t in = j == 0 ? w0 : __ldg(src + (size_t)j * 32);
+            if (j == 0) {
+                v = (in ^ (seq[0] << 7)) & ~0x7fu; /* outputs 0..6 are forced to 0 (decode_impl.cc:315) */
+            } else {
+                int o = (32 * j - 7) % 127;
+                uint32_t s = __funnelshift_r(seq[o >> 5], seq[(o >> 5) + 1], o & 31);
+                v = in ^ s;
+            }
+            int rem = T - 32 * j; /* bits past the trellis are not data */
+            if (rem < 32) v &= (1u << rem) - 1u;
+        }
+        dw[j] = v;
+    }
+    __syncwarp();
+
+    /* PSDU bytes: byte k = bits 16+8k .. 23+8k */
+    const uint8_t* by = reinterpret_cast<const uint8_t*>(dw) + 2;
+    const int navail = T >= 16 ? (T - 16) >> 3 : 0;
+    const int nbytes = d.format == W80211_F_VHT ? navail : min(d.len, navail);
+    const uint32_t poff = psdu_off[pkt];
+    uint32_t* o32 = reinterpret_cast<uint32_t*>(out_bytes + poff);
+    for (int k = lane; k < ((nbytes + 3) >> 2); k += 32) o32[k] = (dw[k] >> 16) | (dw[k + 1] << 16);
+
+    if (d.format != W80211_F_VHT) {
+        if (d.ampdu) return; /* HT A-MPDU: the reference publishes nothing (decode_impl.cc:432-435) */
+        uint32_t crc = warp_crc32(S, by, nbytes, lane);
+        emit(lane, (uint32_t)pkt, poff, (uint32_t)nbytes, nbytes == d.len && crc == CRC_RESIDUE, mpdus, mpdu_cap, counters);
+        return;
+    }
+    /* VHT A-MPDU walk (decode_impl.cc:331-426) */
+    int procd = 16;
+    if (procd >= T) return;
+    int pos = 0, tmplen = 0;
+    for (;;) {
+        procd += 32;
+        if (procd > T) break;
+        uint32_t b0 = by[pos], b1 = by[pos + 1];
+        int eof = b0 & 1u;
+        tmplen |= (int)(((b0 >> 2) & 1u) << 12) | (int)(((b0 >> 3) & 1u) << 13) | (int)(b0 >> 4) | (int)(b1 << 4);
+        int padded = ((tmplen + 3) >> 2) << 2;
+        procd += padded * 8;
+        if (procd > T) break;
+        pos += 4;
+        uint32_t crc = warp_crc32(S, by + pos, tmplen, lane);
+        bool ok = crc == CRC_RESIDUE;
+        emit(lane, (uint32_t)pkt, poff + (uint32_t)pos, (uint32_t)tmplen, ok, mpdus, mpdu_cap, counters);
+        pos += padded;
+        if (ok) tmplen += 4;
+        if (eof) break;
+    }
+}
+
+void w_launch_post(cudaStream_t st, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,
+                   const w80211_desc* desc, const uint32_t* bits, const uint32_t* psdu_off, uint8_t* out_bytes,
+                   w80211_mpdu* mpdus, unsigned int mpdu_cap, unsigned int* counters)
+{
+    if (npkt_dec <= 0) return;
+    int blocks = (npkt_dec + POST_WARPS - 1) / POST_WARPS;
+    post_kernel<<<blocks, POST_WARPS * 32, 0, st>>>(npkt_dec, grp, pkt_slot, dec_list, desc, bits, psdu_off, out_bytes, mpdus,
+                                                    mpdu_cap, counters);
+}

@@ -1,0 +1,189 @@
+/* w80211rx.h -- C ABI of libw80211rx.so: the B200 (sm_100a) implementation of the
+ * gr-ieee80211 receive hot path  demod / demod2  ->  decode.
+ *
+ * This is the drop-in boundary.  The three GNU Radio blocks of the reference
+ *     gr::ieee80211::demod::make(int mupos, int mugid)   include/gnuradio/ieee80211/demod.h:35
+ *     gr::ieee80211::demod2::make()                      include/gnuradio/ieee80211/demod2.h:35
+ *     gr::ieee80211::decode::make(bool ifdebug)          include/gnuradio/ieee80211/decode.h:35
+ * keep their factories, io signatures, tags and messages (gr/ in this repo);
+ * their general_work() bodies gather whole packets and call the entry points
+ * below instead of the per-symbol / per-trellis-step CPU loops
+ *     demod_impl.cc:59-342, demod2_impl.cc:58-349   -> w80211_demod_batch()
+ *     decode_impl.cc:60-520                           -> w80211_decode_batch()
+ * and a batch receiver that keeps the LLRs on the device calls
+ *     w80211_rx_submit() / w80211_rx_collect()        (demod + decode fused, double buffered).
+ *
+ * Conventions: plain C structs, caller owns every host buffer, the library owns
+ * device memory and streams; int return, 0 = ok, < 0 = error (w80211_last_error());
+ * one ctx per GPU; a ctx is used from one thread at a time (GNU Radio calls a
+ * block's general_work from exactly one thread).  There is no CPU fallback:
+ * every entry point fails if no CUDA device is usable.
+ */
+#ifndef W80211RX_H
+#define W80211RX_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define W80211_ABI_VERSION 1
+
+/* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
+#define W80211_F_L 0
+#define W80211_F_HT 1
+#define W80211_F_VHT 2
+/* code rates: C8P_CR_12 .. C8P_CR_56 (lib/cloud80211phy.h:46-49) */
+#define W80211_CR_12 0
+#define W80211_CR_23 1
+#define W80211_CR_34 2
+#define W80211_CR_56 3
+
+/* limits of the reference's decode block (lib/decode_impl.h:35-36) */
+#define W80211_B_MAX 4095
+#define W80211_T_MAX 32782
+
+/* where the caller's sample / LLR / output buffers live */
+#define W80211_MEM_HOST 0   /* host memory (pinned or pageable); copies are part of the call */
+#define W80211_MEM_DEVICE 1 /* device memory of the ctx's GPU; nothing is copied */
+
+/* error codes */
+#define W80211_OK 0
+#define W80211_E_ARG (-1)
+#define W80211_E_CUDA (-2)
+#define W80211_E_NOMEM (-3)
+#define W80211_E_STATE (-4)
+#define W80211_E_CAPACITY (-5)
+
+/* Per-packet verdict of the header stage (format detection, SIG parsing, gates).
+ * Everything but W80211_ST_OK means "the reference's demod goes to its CLEAN state
+ * without emitting LLRs" (demod_impl.cc:159,186) or "outside the scope of this library". */
+#define W80211_ST_OK 0
+#define W80211_ST_DROP_GATE 1    /* len / nSS / L-SIG-duration gate failed (demod_impl.cc:159,186) */
+#define W80211_ST_NDP 2          /* VHT NDP (nSym == 0): demod emits the mu2x1chan tag, no LLRs to decode */
+#define W80211_ST_UNSUPPORTED 3  /* VHT MU group id, VHT MCS > 9: not handled */
+#define W80211_ST_BAD_INPUT 4    /* descriptor inconsistent (nsamp too short for the header fields, l_mcs out of range) */
+
+typedef struct w80211_ctx w80211_ctx;
+
+typedef struct w80211_cfg {
+    int32_t device;        /* CUDA device ordinal */
+    int32_t max_packets;   /* capacity hint per batch (grown on demand) */
+    int32_t nslots;        /* double buffering depth for rx_submit/collect: 1..4 (0 = 2) */
+    int32_t flags;         /* reserved, 0 */
+} w80211_cfg;
+
+/* One packet as the reference's signal / signal2 block hands it over
+ * (tags written at lib/signal_impl.cc:135-152). */
+typedef struct w80211_pkt_in {
+    uint64_t iq_offset; /* index (in samples) of the packet's first sample after L-SIG in every antenna array */
+    int32_t nsamp;      /* tag "nsamp": samples that belong to the packet (without the 320 pad items) */
+    int32_t l_mcs;      /* tag "mcs": legacy rate index 0..7 */
+    int32_t l_len;      /* tag "len": L-SIG LENGTH */
+    float cfo, snr, rssi; /* tags carried through to the output untouched */
+} w80211_pkt_in;
+
+typedef struct w80211_batch_in {
+    int32_t npkt;
+    int32_t nant;            /* 1: demod (lib/demod_impl.cc), 2: demod2 (lib/demod2_impl.cc) */
+    int32_t mem;             /* W80211_MEM_HOST / W80211_MEM_DEVICE: applies to iq[], chan, pkts */
+    int32_t reserved;
+    const float* iq[2];      /* per antenna: interleaved (re,im) fc32 samples */
+    uint64_t nsamples;       /* length of each iq[] array in complex samples */
+    const w80211_pkt_in* pkts; /* [npkt] */
+    const float* chan;       /* [npkt][64][2]: tag "chan", legacy channel in natural FFT order (signal_impl.cc:143) */
+} w80211_batch_in;
+
+/* Per-packet parameters: the reference's c8p_mod (lib/cloud80211phy.h:58-98) plus the
+ * demod->decode tag values (demod_impl.cc:224-253) and where the packet's LLRs are. */
+typedef struct w80211_desc {
+    int32_t status;   /* W80211_ST_* */
+    int32_t format;   /* tag "format" */
+    int32_t mcs;      /* tag "mcs" */
+    int32_t len;      /* tag "len" */
+    int32_t cr;       /* tag "cr" */
+    int32_t ampdu;    /* tag "ampdu" */
+    int32_t trellis;  /* tag "trellis" */
+    int32_t total;    /* tag "total" = nSym * nCBPS */
+    int32_t nss, nltf, nsym, nsymsamp;
+    int32_t mod, nbpscs, ncbpss, ncbps;
+    int32_t ndbps;
+    int32_t data_off; /* first data symbol, in samples from iq_offset */
+    float sssnr0, sssnr1; /* tags "sssnr0"/"sssnr1" (VHT only) */
+    int64_t llr_off;  /* float index of the packet's first LLR in the LLR buffer (multiple of 4) */
+    float cfo, snr, rssi;
+    int32_t l_mcs;    /* copy of the input rate index */
+} w80211_desc;
+
+/* One decoded MPDU (legacy / HT: one per packet; VHT: one per A-MPDU subframe walked). */
+typedef struct w80211_mpdu {
+    uint32_t pkt;     /* packet index in the batch */
+    uint32_t off;     /* byte offset of the MPDU inside out_bytes */
+    uint32_t len;     /* MPDU length in bytes (FCS included) */
+    uint32_t crc_ok;  /* 1: CRC-32 residue == 558161692 (decode_impl.cc:374,453) -> the reference publishes it */
+} w80211_mpdu;
+
+typedef struct w80211_batch_out {
+    int32_t mem;             /* where desc / bytes / mpdus / llr live (HOST or DEVICE); counts are always host */
+    int32_t want_llr;        /* also return the LLR stream (what demod writes to its output port) */
+    w80211_desc* desc;       /* [npkt] */
+    uint8_t* bytes;          /* decoded, descrambled PSDU bytes of all packets, packet p at psdu_off[p] */
+    uint64_t bytes_capacity;
+    uint32_t* psdu_off;      /* [npkt] byte offset of bit 16 (first PSDU byte) of packet p in bytes */
+    w80211_mpdu* mpdus;      /* [mpdu_capacity], sorted by (pkt, off) */
+    uint32_t mpdu_capacity;
+    float* llr;              /* [llr_capacity] or NULL */
+    uint64_t llr_capacity;
+    /* results (host side) */
+    uint32_t n_mpdu;         /* entries written to mpdus */
+    uint32_t n_crc_ok;       /* of which crc_ok */
+    uint64_t n_bytes;        /* bytes used */
+    uint64_t n_llr;          /* floats used */
+    uint64_t psdu_bits_ok;   /* 8 * sum(len of crc_ok MPDUs): the numerator of the throughput metric */
+} w80211_batch_out;
+
+typedef struct w80211_stats {
+    uint64_t packets_in, packets_decoded, dropped_gate, ndp, unsupported, bad_input;
+    uint64_t mpdu_total, mpdu_crc_ok;
+    uint64_t ok_legacy[8], ok_ht[8], ok_vht[10]; /* the counters of decode_impl.h:88-90 */
+    uint64_t trellis_steps;  /* sum of trellis lengths decoded */
+    uint64_t kernel_launches;
+} w80211_stats;
+
+/* Timing of the last completed batch, measured with CUDA events on the ctx's own stream (ms). */
+typedef struct w80211_timing {
+    float h2d, header, demod, viterbi, traceback, post, d2h, total;
+    uint32_t launches; /* kernels launched for that batch */
+} w80211_timing;
+
+int w80211_abi_version(void);
+int w80211_create(const w80211_cfg* cfg, w80211_ctx** out);
+void w80211_destroy(w80211_ctx* ctx);
+const char* w80211_last_error(const w80211_ctx* ctx);
+int w80211_stats_get(const w80211_ctx* ctx, w80211_stats* out);
+int w80211_timing_get(const w80211_ctx* ctx, int slot, w80211_timing* out);
+/* the CUDA stream (cudaStream_t) slot `slot` launches on, for callers that time with their own events */
+void* w80211_stream(const w80211_ctx* ctx, int slot);
+
+/* IQ -> LLR stream + descriptors: what demod / demod2 write to their output port.
+ * out->desc and out->llr are filled; nothing is decoded.  Synchronous. */
+int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out);
+
+/* LLR stream + descriptors -> PSDU bytes + FCS verdicts: what decode does with demod's output.
+ * desc[p].{format,mcs,len,cr,ampdu,trellis,total,llr_off} are read (llr_off may be any float index);
+ * llr_mem says where desc and llr live.  Synchronous. */
+int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, const float* llr,
+                        uint64_t nllr, int32_t llr_mem, w80211_batch_out* out);
+
+/* Fused path: IQ -> bytes, LLRs stay in HBM.  submit() enqueues copies and kernels on slot's stream
+ * and returns; collect() waits for the slot and fills the host-side counters of *out.
+ * rx_batch() = submit + collect on slot 0. */
+int w80211_rx_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w80211_batch_out* out);
+int w80211_rx_collect(w80211_ctx* ctx, int slot);
+int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* W80211RX_H */
