@@ -481,6 +481,21 @@ extern "C" {
 
 int w80211_abi_version(void) { return W80211_ABI_VERSION; }
 
+size_t w80211_sizeof(int what)
+{
+    switch (what) {
+    case 0: return sizeof(w80211_pkt_in);
+    case 1: return sizeof(w80211_batch_in);
+    case 2: return sizeof(w80211_desc);
+    case 3: return sizeof(w80211_mpdu);
+    case 4: return sizeof(w80211_batch_out);
+    case 5: return sizeof(w80211_stats);
+    case 6: return sizeof(w80211_timing);
+    case 7: return sizeof(w80211_cfg);
+    default: return 0;
+    }
+}
+
 int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
 {
     if (!outp) return W80211_E_ARG;

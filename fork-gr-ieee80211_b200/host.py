@@ -1,0 +1,279 @@
+"""ctypes binding of libw80211rx.so (include/w80211rx.h) plus a small convenience layer.
+
+Used by tests/, bench.py and __graft_entry__.py.  Every call goes through the
+C ABI; there is no Python or CPU implementation behind it: if the shared
+library is missing or no CUDA device is usable, `load()` / `Receiver()` raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libw80211rx.so")
+
+MEM_HOST, MEM_DEVICE = 0, 1
+ST_OK, ST_DROP_GATE, ST_NDP, ST_UNSUPPORTED, ST_BAD_INPUT = 0, 1, 2, 3, 4
+F_L, F_HT, F_VHT = 0, 1, 2
+
+SYMBOLS = [
+    "w80211_abi_version", "w80211_sizeof", "w80211_create", "w80211_destroy", "w80211_last_error", "w80211_stats_get",
+    "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
+    "w80211_rx_collect", "w80211_rx_batch",
+]
+
+
+class Cfg(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_packets", C.c_int32), ("nslots", C.c_int32), ("flags", C.c_int32)]
+
+
+class PktIn(C.Structure):
+    _fields_ = [("iq_offset", C.c_uint64), ("nsamp", C.c_int32), ("l_mcs", C.c_int32), ("l_len", C.c_int32),
+                ("cfo", C.c_float), ("snr", C.c_float), ("rssi", C.c_float)]
+
+
+PKT_IN_DTYPE = np.dtype([("iq_offset", "<u8"), ("nsamp", "<i4"), ("l_mcs", "<i4"), ("l_len", "<i4"),
+                         ("cfo", "<f4"), ("snr", "<f4"), ("rssi", "<f4")], align=True)
+
+
+class BatchIn(C.Structure):
+    _fields_ = [("npkt", C.c_int32), ("nant", C.c_int32), ("mem", C.c_int32), ("reserved", C.c_int32),
+                ("iq", C.c_void_p * 2), ("nsamples", C.c_uint64), ("pkts", C.c_void_p), ("chan", C.c_void_p)]
+
+
+DESC_DTYPE = np.dtype([
+    ("status", "<i4"), ("format", "<i4"), ("mcs", "<i4"), ("len", "<i4"), ("cr", "<i4"), ("ampdu", "<i4"),
+    ("trellis", "<i4"), ("total", "<i4"), ("nss", "<i4"), ("nltf", "<i4"), ("nsym", "<i4"), ("nsymsamp", "<i4"),
+    ("mod", "<i4"), ("nbpscs", "<i4"), ("ncbpss", "<i4"), ("ncbps", "<i4"), ("ndbps", "<i4"), ("data_off", "<i4"),
+    ("sssnr0", "<f4"), ("sssnr1", "<f4"), ("llr_off", "<i8"), ("cfo", "<f4"), ("snr", "<f4"), ("rssi", "<f4"),
+    ("l_mcs", "<i4")], align=True)
+
+MPDU_DTYPE = np.dtype([("pkt", "<u4"), ("off", "<u4"), ("len", "<u4"), ("crc_ok", "<u4")])
+
+
+class BatchOut(C.Structure):
+    _fields_ = [("mem", C.c_int32), ("want_llr", C.c_int32), ("desc", C.c_void_p), ("bytes", C.c_void_p),
+                ("bytes_capacity", C.c_uint64), ("psdu_off", C.c_void_p), ("mpdus", C.c_void_p),
+                ("mpdu_capacity", C.c_uint32), ("llr", C.c_void_p), ("llr_capacity", C.c_uint64),
+                ("n_mpdu", C.c_uint32), ("n_crc_ok", C.c_uint32), ("n_bytes", C.c_uint64), ("n_llr", C.c_uint64),
+                ("psdu_bits_ok", C.c_uint64)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("packets_in", C.c_uint64), ("packets_decoded", C.c_uint64), ("dropped_gate", C.c_uint64),
+                ("ndp", C.c_uint64), ("unsupported", C.c_uint64), ("bad_input", C.c_uint64),
+                ("mpdu_total", C.c_uint64), ("mpdu_crc_ok", C.c_uint64), ("ok_legacy", C.c_uint64 * 8),
+                ("ok_ht", C.c_uint64 * 8), ("ok_vht", C.c_uint64 * 10), ("trellis_steps", C.c_uint64),
+                ("kernel_launches", C.c_uint64)]
+
+
+class Timing(C.Structure):
+    _fields_ = [("h2d", C.c_float), ("header", C.c_float), ("demod", C.c_float), ("viterbi", C.c_float),
+                ("traceback", C.c_float), ("post", C.c_float), ("d2h", C.c_float), ("total", C.c_float),
+                ("launches", C.c_uint32)]
+
+
+_lib = None
+
+
+def load():
+    """dlopen the library (no CUDA call yet)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libw80211rx.so is not built: run __graft_entry__.build() (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.w80211_abi_version.restype = C.c_int
+        L.w80211_sizeof.restype = C.c_size_t
+        L.w80211_sizeof.argtypes = [C.c_int]
+        L.w80211_create.argtypes = [C.POINTER(Cfg), C.POINTER(vp)]
+        L.w80211_destroy.argtypes = [vp]
+        L.w80211_destroy.restype = None
+        L.w80211_last_error.argtypes = [vp]
+        L.w80211_last_error.restype = C.c_char_p
+        L.w80211_stats_get.argtypes = [vp, C.POINTER(Stats)]
+        L.w80211_timing_get.argtypes = [vp, C.c_int, C.POINTER(Timing)]
+        L.w80211_stream.argtypes = [vp, C.c_int]
+        L.w80211_stream.restype = vp
+        L.w80211_demod_batch.argtypes = [vp, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+        L.w80211_decode_batch.argtypes = [vp, C.c_int32, vp, vp, C.c_uint64, C.c_int32, C.POINTER(BatchOut)]
+        L.w80211_rx_submit.argtypes = [vp, C.c_int, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+        L.w80211_rx_collect.argtypes = [vp, C.c_int]
+        L.w80211_rx_batch.argtypes = [vp, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+        _lib = L
+    return _lib
+
+
+class W80211Error(RuntimeError):
+    pass
+
+
+def pack_batch(batches):
+    """List of gen_ppdu.gen_batch() dicts (same antenna count) -> (iq list, pkts, chan) numpy arrays:
+    the packets' post-L-SIG samples back to back per antenna, the packet table and the legacy H."""
+    nant = batches[0]["nrx"]
+    iq = [[] for _ in range(nant)]
+    pk, ch = [], []
+    off = 0
+    for b in batches:
+        assert b["nrx"] == nant
+        npkt, nsamp = b["post"][0].shape
+        for a in range(nant):
+            iq[a].append(np.ascontiguousarray(b["post"][a], np.complex64).reshape(-1))
+        t = np.zeros(npkt, PKT_IN_DTYPE)
+        t["iq_offset"] = off + np.arange(npkt, dtype=np.uint64) * nsamp
+        t["nsamp"] = nsamp
+        t["l_mcs"] = b["l_mcs"]
+        t["l_len"] = b["l_len"]
+        pk.append(t)
+        ch.append(np.ascontiguousarray(b["chan"], np.complex64))
+        off += npkt * nsamp
+    return [np.concatenate(x) for x in iq], np.concatenate(pk), np.concatenate(ch)
+
+
+class Result:
+    """Host-side view of one finished batch."""
+
+    def __init__(self, desc, data, psdu_off, mpdus, out, llr=None):
+        self.desc, self.bytes, self.psdu_off, self.mpdus, self.llr = desc, data, psdu_off, mpdus, llr
+        self.n_mpdu, self.n_crc_ok, self.psdu_bits_ok = out.n_mpdu, out.n_crc_ok, out.psdu_bits_ok
+        self.n_llr, self.n_bytes = out.n_llr, out.n_bytes
+
+    def messages(self):
+        """The blobs the reference's decode block publishes (decode_impl.cc:439-441, 512-516), in order:
+        [format, len & 0xff, len >> 8, MPDU bytes, mcs] for every FCS-valid MPDU."""
+        out = []
+        for m in self.mpdus[: self.n_mpdu]:
+            if not m["crc_ok"]:
+                continue
+            d = self.desc[m["pkt"]]
+            ln = int(m["len"])
+            body = self.bytes[m["off"]: m["off"] + ln].tobytes()
+            out.append(bytes([int(d["format"]), ln & 0xFF, ln >> 8]) + body + bytes([int(d["mcs"]) & 0xFF]))
+        return out
+
+    def packet_llr(self, p):
+        d = self.desc[p]
+        return self.llr[d["llr_off"]: d["llr_off"] + d["total"]]
+
+
+class Receiver:
+    """One w80211_ctx (one GPU)."""
+
+    def __init__(self, device=0, nslots=2):
+        self.L = load()
+        self.h = C.c_void_p()
+        cfg = Cfg(device, 0, nslots, 0)
+        r = self.L.w80211_create(C.byref(cfg), C.byref(self.h))
+        if r != 0:
+            raise W80211Error("w80211_create failed (%d): no usable CUDA device; this library has no CPU path" % r)
+        self._keep = {}
+
+    def close(self):
+        if self.h:
+            self.L.w80211_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, r):
+        if r != 0:
+            raise W80211Error("%d: %s" % (r, self.L.w80211_last_error(self.h).decode()))
+
+    # -- raw struct helpers -------------------------------------------------
+    @staticmethod
+    def make_in(iq, pkts, chan, mem=MEM_HOST, nsamples=None, npkt=None):
+        """iq: list of numpy complex64 arrays (host) or integer device pointers (device)."""
+        bi = BatchIn()
+        bi.nant = len(iq)
+        bi.mem = mem
+        if mem == MEM_HOST:
+            bi.npkt = len(pkts)
+            bi.nsamples = len(iq[0])
+            for a, x in enumerate(iq):
+                assert x.dtype == np.complex64 and x.flags.c_contiguous
+                bi.iq[a] = x.ctypes.data
+            assert pkts.dtype == PKT_IN_DTYPE
+            bi.pkts = pkts.ctypes.data
+            assert chan.dtype == np.complex64 and chan.flags.c_contiguous
+            bi.chan = chan.ctypes.data
+        else:
+            bi.npkt = npkt
+            bi.nsamples = nsamples
+            for a, x in enumerate(iq):
+                bi.iq[a] = int(x)
+            bi.pkts = int(pkts)
+            bi.chan = int(chan)
+        return bi
+
+    @staticmethod
+    def make_out_host(npkt, bytes_cap, mpdu_cap, llr_cap=0):
+        bo = BatchOut()
+        arrs = {
+            "desc": np.zeros(npkt, DESC_DTYPE),
+            "bytes": np.zeros(max(bytes_cap, 16), np.uint8),
+            "psdu_off": np.zeros(max(npkt, 1), np.uint32),
+            "mpdus": np.zeros(max(mpdu_cap, 1), MPDU_DTYPE),
+            "llr": np.zeros(max(llr_cap, 4), np.float32) if llr_cap else None,
+        }
+        bo.mem = MEM_HOST
+        bo.desc = arrs["desc"].ctypes.data
+        bo.bytes = arrs["bytes"].ctypes.data
+        bo.bytes_capacity = arrs["bytes"].size
+        bo.psdu_off = arrs["psdu_off"].ctypes.data
+        bo.mpdus = arrs["mpdus"].ctypes.data
+        bo.mpdu_capacity = arrs["mpdus"].size
+        if llr_cap:
+            bo.want_llr = 1
+            bo.llr = arrs["llr"].ctypes.data
+            bo.llr_capacity = arrs["llr"].size
+        return bo, arrs
+
+    # -- convenience --------------------------------------------------------
+    def _caps(self, iq, pkts):
+        nsamp_tot = int(pkts["nsamp"].astype(np.int64).sum()) if len(pkts) else 0
+        # decoded bytes < 1 per sample (2 streams of 256-QAM 5/6: 86 B per 80 samples); LLR floats <= 832 per 72 samples
+        return nsamp_tot * 2 + 64 * len(pkts) + 64, len(pkts) * 2 + nsamp_tot // 64 + 64, \
+            nsamp_tot * 12 + 64 * len(pkts) + 64
+
+    def rx(self, iq, pkts, chan, want_llr=False):
+        """IQ -> bytes, fused (w80211_rx_batch)."""
+        bcap, mcap, lcap = self._caps(iq, pkts)
+        bi = self.make_in(iq, pkts, chan)
+        bo, arrs = self.make_out_host(len(pkts), bcap, mcap, lcap if want_llr else 0)
+        self._check(self.L.w80211_rx_batch(self.h, C.byref(bi), C.byref(bo)))
+        return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo, arrs["llr"])
+
+    def demod(self, iq, pkts, chan):
+        """IQ -> LLR stream + descriptors (w80211_demod_batch): what demod / demod2 output."""
+        bcap, mcap, lcap = self._caps(iq, pkts)
+        bi = self.make_in(iq, pkts, chan)
+        bo, arrs = self.make_out_host(len(pkts), 16, 1, lcap)
+        self._check(self.L.w80211_demod_batch(self.h, C.byref(bi), C.byref(bo)))
+        return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo, arrs["llr"])
+
+    def decode(self, desc, llr):
+        """LLR stream + descriptors -> bytes (w80211_decode_batch): what decode does."""
+        desc = np.ascontiguousarray(desc, DESC_DTYPE)
+        llr = np.ascontiguousarray(llr, np.float32)
+        npkt = len(desc)
+        bcap = int(np.maximum(desc["trellis"], 0).astype(np.int64).sum()) // 8 + 64 * npkt + 64
+        bo, arrs = self.make_out_host(npkt, bcap, npkt * 2 + bcap // 32 + 64)
+        self._check(self.L.w80211_decode_batch(self.h, npkt, desc.ctypes.data, llr.ctypes.data, llr.size, MEM_HOST,
+                                               C.byref(bo)))
+        return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo)
+
+    def stats(self):
+        s = Stats()
+        self._check(self.L.w80211_stats_get(self.h, C.byref(s)))
+        return s
+
+    def timing(self, slot=0):
+        t = Timing()
+        self._check(self.L.w80211_timing_get(self.h, slot, C.byref(t)))
+        return t

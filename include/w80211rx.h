@@ -158,6 +158,9 @@ typedef struct w80211_timing {
 } w80211_timing;
 
 int w80211_abi_version(void);
+/* sizeof of the ABI structs as compiled: 0 pkt_in, 1 batch_in, 2 desc, 3 mpdu, 4 batch_out, 5 stats, 6 timing, 7 cfg
+ * (lets a binding written in another language check its own layout) */
+size_t w80211_sizeof(int what);
 int w80211_create(const w80211_cfg* cfg, w80211_ctx** out);
 void w80211_destroy(w80211_ctx* ctx);
 const char* w80211_last_error(const w80211_ctx* ctx);

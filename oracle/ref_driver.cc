@@ -246,5 +246,51 @@ void ref_sv_tables(int* next128, int* output128)
         }
 }
 void ref_pilot_p(float* out127) { memcpy(out127, PILOT_P, sizeof(float) * 127); }
+/* Read-only views of the reference's constant tables, for tests/test_tables.py.
+ * Returns the number of entries written (as doubles), 0 for an unknown name. */
+int ref_table(const char* name, double* out, int maxn)
+{
+    std::string k(name);
+    const int* ip = nullptr;
+    const float* fp = nullptr;
+    int n = 0;
+    if (k == "mapDeintLegacyBpsk") { ip = mapDeintLegacyBpsk; n = 48; }
+    else if (k == "mapDeintLegacyQpsk") { ip = mapDeintLegacyQpsk; n = 96; }
+    else if (k == "mapDeintLegacy16Qam") { ip = mapDeintLegacy16Qam; n = 192; }
+    else if (k == "mapDeintLegacy64Qam") { ip = mapDeintLegacy64Qam; n = 288; }
+    else if (k == "mapDeintNonlegacyBpsk") { ip = mapDeintNonlegacyBpsk; n = 52; }
+    else if (k == "mapDeintNonlegacyQpsk") { ip = mapDeintNonlegacyQpsk; n = 104; }
+    else if (k == "mapDeintNonlegacy16Qam") { ip = mapDeintNonlegacy16Qam; n = 208; }
+    else if (k == "mapDeintNonlegacy64Qam") { ip = mapDeintNonlegacy64Qam; n = 312; }
+    else if (k == "mapDeintNonlegacy256Qam") { ip = mapDeintNonlegacy256Qam; n = 416; }
+    else if (k == "mapDeintVhtSigB20") { ip = mapDeintVhtSigB20; n = 52; }
+    else if (k == "LTF_NL_28_F_FLOAT") { fp = LTF_NL_28_F_FLOAT; n = 64; }
+    else if (k == "LTF_NL_28_F_FLOAT2") { fp = LTF_NL_28_F_FLOAT2; n = 64; }
+    else if (k == "PILOT_P") { fp = PILOT_P; n = 127; }
+    if (n > maxn) n = maxn;
+    for (int i = 0; i < n; i++) out[i] = ip ? (double)ip[i] : (double)fp[i];
+    return n;
+}
+void ref_intel_vhtb20(const uint8_t* in52, uint8_t* out52)
+{
+    uint8_t tmp[52];
+    memcpy(tmp, in52, 52);
+    procIntelVhtB20(tmp, out52);
+}
+/* procNLSigDemodDeint (cloud80211phy.cc:629-648) on caller-supplied FFT bins */
+void ref_nlsig_demod(const float* sym1, const float* sym2, const float* h, float* llrht96, float* llrvht96)
+{
+    std::vector<gr_complex> s1(64), s2(64), hh(64);
+    memcpy(s1.data(), sym1, 512);
+    memcpy(s2.data(), sym2, 512);
+    memcpy(hh.data(), h, 512);
+    procNLSigDemodDeint(s1.data(), s2.data(), hh, llrht96, llrvht96);
+}
+int ref_check_crc8(const uint8_t* bits42)
+{
+    uint8_t tmp[42];
+    memcpy(tmp, bits42, 42);
+    return checkBitCrc8(tmp, 34, &tmp[34]) ? 1 : 0;
+}
 
 } /* extern "C" */

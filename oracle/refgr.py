@@ -66,6 +66,10 @@ def lib():
         L.ref_bcc_encode.argtypes = [vp, vp, ci]
         L.ref_sv_tables.argtypes = [vp, vp]
         L.ref_pilot_p.argtypes = [vp]
+        L.ref_table.argtypes = [C.c_char_p, vp, ci]
+        L.ref_intel_vhtb20.argtypes = [vp, vp]
+        L.ref_check_crc8.argtypes = [vp]
+        L.ref_nlsig_demod.argtypes = [vp, vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -321,3 +325,32 @@ def sv_tables():
     op = np.zeros(128, np.int32)
     lib().ref_sv_tables(nx.ctypes.data, op.ctypes.data)
     return nx.reshape(64, 2), op.reshape(64, 2)
+
+
+def table(name):
+    """One of the reference's constant tables (cloud80211phy.cc) as a float64 array."""
+    out = np.zeros(512, np.float64)
+    n = lib().ref_table(name.encode(), out.ctypes.data, out.size)
+    if n == 0:
+        raise KeyError(name)
+    return out[:n].copy()
+
+
+def intel_vhtb20(bits52):
+    b = np.ascontiguousarray(bits52, np.uint8)
+    out = np.zeros(52, np.uint8)
+    lib().ref_intel_vhtb20(b.ctypes.data, out.ctypes.data)
+    return out
+
+
+def check_crc8(bits42):
+    b = np.ascontiguousarray(bits42, np.uint8)
+    return bool(lib().ref_check_crc8(b.ctypes.data))
+
+
+def nlsig_demod(sym1, sym2, h):
+    a = [np.ascontiguousarray(x, np.complex64) for x in (sym1, sym2, h)]
+    ht = np.zeros(96, np.float32)
+    vht = np.zeros(96, np.float32)
+    lib().ref_nlsig_demod(a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data, ht.ctypes.data, vht.ctypes.data)
+    return ht, vht

@@ -1,0 +1,131 @@
+"""CPU tests: the tables libw80211rx generates from the 802.11 formulas equal the reference's arrays
+(cloud80211phy.cc), the C-ABI library loads and exports every symbol of include/w80211rx.h, and the
+ABI struct layouts of the Python binding match the compiled ones.  No GPU needed."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import w80211rx
+
+host = w80211rx.host
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+TAB_DTYPE = np.dtype([("pilot_p", "<f4", 128), ("ltf_nl", "<f4", 64), ("sig_demap", "i1", 64), ("bin_j_l", "i1", 64),
+                      ("bin_j_nl", "i1", 64), ("sigb_deint", "u1", 52), ("sigb_int", "u1", 52),
+                      ("map", "<u2", (19, 416))], align=True)
+
+
+@pytest.fixture(scope="module")
+def tab():
+    L = host.load()
+    t = np.zeros(1, TAB_DTYPE)
+    L.w80211_fill_tables.argtypes = [C.c_void_p]
+    L.w80211_fill_tables.restype = None
+    L.w80211_fill_tables(t.ctypes.data)
+    return t[0]
+
+
+def test_library_exports_every_declared_symbol():
+    L = host.load()
+    hdr = open(os.path.join(ROOT, "include", "w80211rx.h")).read()
+    declared = set(re.findall(r"\b(w80211_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(host.SYMBOLS), declared ^ set(host.SYMBOLS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.w80211_abi_version() == 1
+
+
+def test_struct_layouts_match():
+    L = host.load()
+    sizes = [L.w80211_sizeof(i) for i in range(8)]
+    mine = [C.sizeof(host.PktIn), C.sizeof(host.BatchIn), host.DESC_DTYPE.itemsize, host.MPDU_DTYPE.itemsize,
+            C.sizeof(host.BatchOut), C.sizeof(host.Stats), C.sizeof(host.Timing), C.sizeof(host.Cfg)]
+    assert sizes == mine
+    assert host.PKT_IN_DTYPE.itemsize == sizes[0]
+
+
+def test_no_cuda_device_fails_loudly():
+    """There is no CPU path: without a GPU the context cannot be created."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(host.W80211Error):
+        host.Receiver(0)
+
+
+def test_pilot_and_ltf(tab, refgr):
+    assert np.array_equal(tab["pilot_p"][:127], refgr.table("PILOT_P").astype(np.float32))
+    assert np.array_equal(tab["ltf_nl"], refgr.table("LTF_NL_28_F_FLOAT").astype(np.float32))
+    assert np.array_equal(tab["ltf_nl"] * np.float32(0.5), refgr.table("LTF_NL_28_F_FLOAT2").astype(np.float32))
+
+
+def test_data_deinterleave_maps(tab, refgr):
+    names = ["mapDeintLegacyBpsk", "mapDeintLegacyQpsk", "mapDeintLegacy16Qam", "mapDeintLegacy64Qam",
+             "mapDeintNonlegacyBpsk", "mapDeintNonlegacyQpsk", "mapDeintNonlegacy16Qam", "mapDeintNonlegacy64Qam",
+             "mapDeintNonlegacy256Qam"]
+    for i, n in enumerate(names):
+        ref = refgr.table(n).astype(np.int64)
+        assert np.array_equal(tab["map"][i][: len(ref)].astype(np.int64), ref), n
+
+
+def test_two_stream_maps_equal_deinterleave_plus_deparse(tab, refgr):
+    """map[9+a] / map[14+a] fold procSymDeintNL2SS1/SS2 and procSymDepasNL into one scatter."""
+    for a, nb in enumerate([1, 2, 4, 6, 8]):
+        n = 52 * nb
+        x0 = np.arange(n, dtype=np.float32) + 1.0
+        x1 = np.arange(n, dtype=np.float32) + 1001.0
+        ref = refgr.depas2(nb, refgr.deint(1, x0), refgr.deint(2, x1))
+        mine = np.zeros(2 * n, np.float32)
+        mine[tab["map"][9 + a][:n]] = x0
+        mine[tab["map"][14 + a][:n]] = x1
+        assert np.array_equal(mine, ref), nb
+
+
+def test_sig_maps(tab, refgr):
+    assert np.array_equal(tab["sigb_deint"].astype(np.int64), refgr.table("mapDeintVhtSigB20").astype(np.int64))
+    ramp = (np.arange(52) % 2).astype(np.uint8)
+    for seed in range(4):
+        bits = np.random.default_rng(seed).integers(0, 2, 52, dtype=np.uint8)
+        mine = np.zeros(52, np.uint8)
+        mine[tab["sigb_int"]] = bits
+        assert np.array_equal(mine, refgr.intel_vhtb20(bits))
+    # SIG demap through procNLSigDemodDeint with h = 1 and pilots giving a unit phase reference
+    sym = np.zeros(64, np.complex64)
+    sym[[7, 43, 57]] = 1.0
+    sym[21] = -1.0
+    used = np.flatnonzero(tab["sig_demap"] >= 0)
+    assert len(used) == 48
+    sym[used] = (used + 1) * 1j  # imaginary part carries the bin number
+    ht, vht = refgr.nlsig_demod(sym, sym, np.ones(64, np.complex64))
+    for k in used:
+        assert ht[tab["sig_demap"][k]] == k + 1 and ht[tab["sig_demap"][k] + 48] == k + 1
+
+
+def test_bin_to_subcarrier_index(tab):
+    # ascending frequency, pilots and DC removed: legacy -26..26 -> 0..47, HT/VHT -28..28 -> 0..51
+    for name, half, n in (("bin_j_l", 26, 48), ("bin_j_nl", 28, 52)):
+        want = {}
+        j = 0
+        for k in range(-half, half + 1):
+            if k in (0, -21, -7, 7, 21):
+                continue
+            want[k % 64] = j
+            j += 1
+        assert j == n
+        for b in range(64):
+            assert tab[name][b] == want.get(b, -1)
+
+
+def test_branch_labels_match_reference(refgr):
+    """w_branch_label() (common.cuh) restated here must equal SV_STATE_OUTPUT; next-state rule too."""
+    nx, op = refgr.sv_tables()
+    for st in range(64):
+        for b in range(2):
+            x = [(st >> (5 - i)) & 1 for i in range(6)]  # x[0] = newest
+            A = b ^ x[1] ^ x[2] ^ x[4] ^ x[5]
+            B = b ^ x[0] ^ x[1] ^ x[2] ^ x[5]
+            assert op[st][b] == (A << 1 | B)
+            assert nx[st][b] == (st >> 1) | (b << 5)

@@ -1,0 +1,56 @@
+"""Helpers shared by the parity tests: run the reference chain (oracle/_ref) and compare."""
+import numpy as np
+
+import w80211rx
+
+gp = w80211rx.gen_ppdu
+host = w80211rx.host
+
+TAG_KEYS = ("format", "mcs", "len", "cr", "ampdu", "trellis", "total")
+
+
+def ref_chain(refgr, batches, debug=False):
+    """-> (list of per-packet dicts from the reference demod's output stream, list of published blobs)."""
+    nant = batches[0]["nrx"]
+    pk = []
+    for b in batches:
+        pk += gp.to_packets(b)
+    for i, p in enumerate(pk):
+        p["seq"] = i
+    streams = refgr.make_sig_stream(pk, nant=nant)
+    llr = refgr.run_demod(streams)
+    pkts = refgr.split_llr_stream(llr)
+    msgs = refgr.run_decode(llr, debug=debug)
+    return pkts, msgs
+
+
+def llr_close(a, b, scale):
+    """|a-b| <= 1e-4 * max(|a|,|b|,scale): the tolerance of BASELINE.json, SURVEY.md 7.3-5."""
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return np.all(np.abs(a - b) <= 1e-4 * np.maximum(np.maximum(np.abs(a), np.abs(b)), scale))
+
+
+def compare_with_reference(refgr, rx, batches, exact_llr=True):
+    """Run both sides on the same samples and assert tags, LLRs and published messages agree.
+    Returns (our Result, reference messages)."""
+    iq, pkts, chan = host.pack_batch(batches)
+    res = rx.rx(iq, pkts, chan, want_llr=True)
+    ref_pkts, ref_msgs = ref_chain(refgr, batches)
+    ok_idx = [p for p in range(len(pkts)) if res.desc[p]["status"] == host.ST_OK]
+    assert len(ok_idx) == len(ref_pkts), "packets that reach the demod loop: %d vs reference %d" % (len(ok_idx), len(ref_pkts))
+    for p, r in zip(ok_idx, ref_pkts):
+        d = res.desc[p]
+        for k in TAG_KEYS:
+            assert int(d[k]) == int(r[k]), "packet %d tag %s: %d vs reference %d" % (p, k, d[k], r[k])
+        mine = res.packet_llr(p)
+        assert mine.shape == r["llr"].shape
+        scale = {1: 1.0, 2: 1.0, 4: 2.0, 6: 4.0, 8: 8.0}[int(d["nbpscs"])]
+        assert llr_close(mine, r["llr"], scale), "packet %d LLRs differ by more than 1e-4 relative" % p
+        if exact_llr:
+            nd = int((mine != r["llr"]).sum())
+            assert nd == 0, "packet %d: %d LLRs not bit-identical to the reference" % (p, nd)
+        if int(d["format"]) == host.F_VHT:
+            assert abs(float(d["sssnr0"]) - float(r["sssnr0"])) <= 1e-3 * max(1.0, abs(float(r["sssnr0"])))
+    assert res.messages() == ref_msgs, "published messages differ (%d vs %d)" % (len(res.messages()), len(ref_msgs))
+    return res, ref_msgs
