@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- decoded PSDU throughput of the demod + decode hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[3], the configuration the 50 Gbit/s target is quoted on):
+VHT MCS8 (256-QAM r3/4), 1 spatial stream, long GI, APEP 4092 (one 4088-byte MPDU per A-MPDU),
+AWGN at 30 dB, synthetic.  A step is one pass of the whole path (header, demod, Viterbi, traceback,
+descramble + FCS) over one batch of packets.  `value` is measured with the batch already in HBM;
+`e2e` goes through the C ABI with host buffers (pinned), copies inside the timed region.
+One JSON line on stdout (rank 0).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "decoded_psdu_gbit_per_s"
+UNIT = "Gbit/s"
+WORKLOAD = "C4: VHT MCS8 256-QAM r3/4 1SS long-GI, APEP 4092 B (MPDU 4088 B), AWGN 30 dB, 20 MHz"
+MPDU_LEN = 4088
+N_UNIQUE = 512
+
+
+def gen_unique(n, seed):
+    import w80211rx
+    gp, g = w80211rx.gen_ppdu, w80211rx.gen
+    return gp.gen_batch(g.F_VHT, 8, 1, MPDU_LEN, n, snr_db=30, seed=seed)
+
+
+# ------------------------------------------------------------------ reference arm
+def _ref_worker(args):
+    """One oracle instance (the reference's blocks compiled unchanged) over its own packets."""
+    seed, npkt = args
+    from oracle import refgr
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from util import ref_chain
+    b = gen_unique(npkt, seed)
+    t0 = time.perf_counter()
+    _, msgs = ref_chain(refgr, [b])
+    dt = time.perf_counter() - t0
+    ok = sum(1 for m, x in zip(msgs, b["mpdu"]) if m[3:-1] == x.tobytes())
+    return dt, ok, npkt
+
+
+def run_reference_sample(cores, pkts_per_core, seed0=1000):
+    """-> (Gbit/s over all cores, packets ok, packets, wall seconds)."""
+    import multiprocessing as mp
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores) as pool:
+        t0 = time.perf_counter()
+        res = pool.map(_ref_worker, [(seed0 + i, pkts_per_core) for i in range(cores)])
+        wall = time.perf_counter() - t0
+    ok = sum(r[1] for r in res)
+    n = sum(r[2] for r in res)
+    slowest = max(r[0] for r in res)  # decode time only (generation excluded), cores run side by side
+    return ok * MPDU_LEN * 8 / slowest / 1e9, ok, n, slowest, wall
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import refgr
+    if not refgr.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref80211.so missing (build() makes it where /root/reference is mounted)"}))
+        return 0
+    cores = host_cores()
+    per_core = args.ref_packets
+    for _ in range(max(args.warmup, 0)):
+        run_reference_sample(cores, 1)
+    vals, tot_ok, tot_n, tsum = [], 0, 0, 0.0
+    for k in range(args.steps):
+        gbps, ok, n, slowest, _ = run_reference_sample(cores, per_core, 2000 + 100 * k)
+        vals.append(gbps)
+        tot_ok += ok
+        tot_n += n
+        tsum += slowest
+    value = tot_ok * MPDU_LEN * 8 / tsum / 1e9
+    sample = "%d cores x %d packets per step, %d steps; reference blocks (demod + decode) built unchanged, mock scheduler" % (cores, per_core, args.steps)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tsum / max(args.steps, 1), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "packets_per_step": cores * per_core},
+            "packets_per_s": tot_ok / tsum, "fcs_ok": tot_ok, "packets": tot_n,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([x.strip() for x in ln.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                pass
+        sm = [float(r[0]) for r in self.rows if len(r) >= 8 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) >= 8:
+                for i, nm in enumerate(names):
+                    if r[4 + i].lower().startswith("active"):
+                        reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ our arm
+def main_gpu(args):
+    import torch
+    import w80211rx
+    host = w80211rx.host
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    P = args.packets
+    # ---- synthetic batch: N_UNIQUE distinct packets (own seed per rank), tiled to P packets per step
+    ub = gen_unique(N_UNIQUE, 4 + 17 * rank)
+    iq_u, pk_u, ch_u = host.pack_batch([ub])
+    nsamp = int(pk_u["nsamp"][0])
+    reps = (P + N_UNIQUE - 1) // N_UNIQUE
+    pk = np.zeros(P, host.PKT_IN_DTYPE)
+    pk["iq_offset"] = np.arange(P, dtype=np.uint64) * nsamp
+    pk["nsamp"] = nsamp
+    pk["l_mcs"] = pk_u["l_mcs"][0]
+    pk["l_len"] = pk_u["l_len"][0]
+    chan = np.ascontiguousarray(np.tile(ch_u, (reps, 1))[:P])
+    # host copy (pinned) for the end-to-end leg, device copy for the resident leg
+    iq_host = torch.empty(P * nsamp, dtype=torch.complex64).pin_memory()
+    src = torch.from_numpy(iq_u[0])
+    for r in range(reps):
+        n = min(N_UNIQUE, P - r * N_UNIQUE) * nsamp
+        iq_host[r * N_UNIQUE * nsamp: r * N_UNIQUE * nsamp + n] = src[:n]
+    pk_host = torch.from_numpy(pk.view(np.uint8).copy()).pin_memory()
+    ch_host = torch.from_numpy(chan.view(np.float32).reshape(-1).copy()).pin_memory()
+    iq_dev = iq_host.to(dev)
+    pk_dev = pk_host.to(dev)
+    ch_dev = ch_host.to(dev)
+
+    rx = host.Receiver(local, nslots=2)
+    bytes_cap = P * 4160 + 4096
+    mp_cap = 2 * P + 64
+
+    def dev_out():
+        t = {"desc": torch.empty(P * host.DESC_DTYPE.itemsize, dtype=torch.uint8, device=dev),
+             "bytes": torch.empty(bytes_cap, dtype=torch.uint8, device=dev),
+             "psdu_off": torch.empty(P, dtype=torch.int32, device=dev),
+             "mpdus": torch.empty(mp_cap * 16, dtype=torch.uint8, device=dev)}
+        bo = host.BatchOut()
+        bo.mem = host.MEM_DEVICE
+        bo.desc, bo.bytes, bo.bytes_capacity = t["desc"].data_ptr(), t["bytes"].data_ptr(), bytes_cap
+        bo.psdu_off, bo.mpdus, bo.mpdu_capacity = t["psdu_off"].data_ptr(), t["mpdus"].data_ptr(), mp_cap
+        return bo, t
+
+    def host_out():
+        t = {"desc": torch.empty(P * host.DESC_DTYPE.itemsize, dtype=torch.uint8).pin_memory(),
+             "bytes": torch.empty(bytes_cap, dtype=torch.uint8).pin_memory(),
+             "psdu_off": torch.empty(P, dtype=torch.int32).pin_memory(),
+             "mpdus": torch.empty(mp_cap * 16, dtype=torch.uint8).pin_memory()}
+        bo = host.BatchOut()
+        bo.mem = host.MEM_HOST
+        bo.desc, bo.bytes, bo.bytes_capacity = t["desc"].data_ptr(), t["bytes"].data_ptr(), bytes_cap
+        bo.psdu_off, bo.mpdus, bo.mpdu_capacity = t["psdu_off"].data_ptr(), t["mpdus"].data_ptr(), mp_cap
+        return bo, t
+
+    bi_dev = host.Receiver.make_in([iq_dev.data_ptr()], pk_dev.data_ptr(), ch_dev.data_ptr(), mem=host.MEM_DEVICE,
+                                   nsamples=P * nsamp, npkt=P)
+    bi_host = host.Receiver.make_in([iq_host.data_ptr()], pk_host.data_ptr(), ch_host.data_ptr(), mem=host.MEM_DEVICE,
+                                    nsamples=P * nsamp, npkt=P)
+    bi_host.mem = host.MEM_HOST
+    bo_dev, keep_dev = dev_out()
+    bo_h = [host_out() for _ in range(2)]
+    L, h = rx.L, rx.h
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        rx._check(L.w80211_rx_submit(h, 0, C.byref(bi_dev), C.byref(bo_dev)))
+        rx._check(L.w80211_rx_collect(h, 0))
+        return bo_dev.psdu_bits_ok, bo_dev.n_crc_ok
+
+    # ---- resident leg: W warm-up + K timed steps, sequential on slot 0 (clean per-stage events)
+    for _ in range(args.warmup):
+        step_resident()
+    clocks = ClockSampler(local)
+    clocks.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    bits = npk_ok = launches = 0
+    stage = {k: 0.0 for k in ("header", "demod", "viterbi", "traceback", "post", "total")}
+    for _ in range(args.steps):
+        b, n = step_resident()
+        bits += b
+        npk_ok += n
+        t = rx.timing(0)
+        launches += t.launches
+        for k in stage:
+            stage[k] += getattr(t, k)
+    barrier()
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+
+    # ---- end-to-end leg: host buffers -> C ABI -> host results, two slots in flight
+    def e2e_run(nsteps):
+        tot = 0
+        pend = []
+        for i in range(nsteps):
+            s = i & 1
+            if len(pend) == 2:
+                ps = pend.pop(0)
+                rx._check(L.w80211_rx_collect(h, ps))
+                tot += bo_h[ps][0].psdu_bits_ok
+            rx._check(L.w80211_rx_submit(h, s, C.byref(bi_host), C.byref(bo_h[s][0])))
+            pend.append(s)
+        for ps in pend:
+            rx._check(L.w80211_rx_collect(h, ps))
+            tot += bo_h[ps][0].psdu_bits_ok
+        return tot
+
+    e2e_run(max(2, min(args.warmup, 3)))
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    e2e_bits = e2e_run(args.steps)
+    barrier()
+    f1.record()
+    f1.synchronize()
+    e2e_ms = f0.elapsed_time(f1)
+    h2d = P * nsamp * 8 + pk_host.numel() + ch_host.numel() * 4
+    d2h = int(bo_h[0][0].n_bytes) + int(bo_h[0][0].n_mpdu) * 16 + 64 + P * host.DESC_DTYPE.itemsize
+
+    # ---- max over ranks, totals over ranks
+    vals = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
+    sums = torch.tensor([float(bits), float(npk_ok), float(e2e_bits), float(launches)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    ms, e2e_ms = vals.tolist()
+    bits, npk_ok, e2e_bits, launches = sums.tolist()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    K = args.steps
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s"
+    # dominant kernel: the Viterbi forward pass.  Algorithmic bytes per trellis step: LLRs read
+    # (total*4/trellis = 5.33 B at rate 3/4) + one 64-bit survivor word written.
+    st = rx.stats()
+    steps_per_launch = 32760.0 * P
+    vit_ms = stage["viterbi"] / K
+    alg_bytes = steps_per_launch * (43680.0 * 4 / 32760.0 + 8.0)
+    achieved = alg_bytes / (vit_ms * 1e-3) / 1e9
+    sm_clk = clk["sm_mhz"] or float(peaks.get("sm_max_mhz", 1965.0))
+    acs_per_s = steps_per_launch * 64 / (vit_ms * 1e-3)
+    acs_peak = 148 * 128 * sm_clk * 1e6 / 3.0
+    demod_ms = stage["demod"] / K
+    demod_bytes = P * 105.0 * (80 * 8 + 416 * 4)
+    line = {
+        "metric": METRIC, "value": bits / (ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "packets_per_step_per_gpu": P, "unique_packets": N_UNIQUE,
+                   "l2": "inputs larger than L2 (%.1f GB of IQ per step)" % (P * nsamp * 8 / 1e9), "parallelism": "packets sharded by rank, no collective"},
+        "packets_per_s": npk_ok / (ms * 1e-3), "fcs_ok_per_step": npk_ok / K / world,
+        "e2e": {"value": e2e_bits / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": e2e_ms / K, "note": "pinned host buffers through w80211_rx_submit/collect, 2 slots in flight"},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "stage_ms_per_step": {k: v / K for k, v in stage.items()},
+        "roofline": {"bound": "hbm", "kernel": "viterbi_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                     "note": "the kernel is FP32/ALU issue bound, not HBM bound: see roofline_compute"},
+        "roofline_compute": {"kernel": "viterbi_kernel", "bound": "fp32+alu issue", "achieved": acs_per_s / 1e12, "peak": acs_peak / 1e12,
+                             "unit": "T ACS/s", "frac": acs_per_s / acs_peak,
+                             "peak_def": "148 SMs x 128 lanes x SM clock under load / 3 lane-ops per ACS (SURVEY.md 8(d))", "sm_mhz": sm_clk},
+        "roofline_demod": {"kernel": "demod_kernel", "bound": "hbm", "achieved": demod_bytes / (demod_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                           "unit": "GB/s", "frac": demod_bytes / (demod_ms * 1e-3) / 1e9 / hbm_peak},
+    }
+    # ---- CPU baseline beside it (rank 0, N = 1 only): the reference's own blocks on the host cores
+    if world == 1 and not args.no_cpu:
+        from oracle import refgr
+        if refgr.available():
+            cores = host_cores()
+            gbps, ok, n, slowest, wall = run_reference_sample(cores, args.ref_packets)
+            line["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": cores, "kind": "reference",
+                                    "sample": "%d packets of the same workload per core on %d cores, %.1f s; reference demod + decode blocks built unchanged (oracle/_ref), mock scheduler; %d/%d FCS ok"
+                                              % (args.ref_packets, cores, slowest, ok, n)}
+    print(json.dumps(line))
+    rx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--packets", type=int, default=int(os.environ.get("W80211_BENCH_PACKETS", "32768")))
+    ap.add_argument("--ref-packets", type=int, default=96, help="packets per core and step for the CPU reference")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return main_reference(args)
+    return main_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,174 @@
+"""More GPU parity: the reference's golden fixtures, 2x2, drop gates, ragged / empty batches,
+A-MPDUs with several subframes, the split demod / decode entry points, and size-independent
+properties at full batch size."""
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+import w80211rx
+from util import compare_with_reference, ref_chain
+
+gp, g, host = w80211rx.gen_ppdu, w80211rx.gen, w80211rx.host
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def golden_inputs(name):
+    z = np.load(os.path.join(GOLD, name))
+    post = z["post"]
+    pk = np.zeros(1, host.PKT_IN_DTYPE)
+    pk["nsamp"] = post.shape[1]
+    pk["l_mcs"] = int(z["l_mcs"])
+    pk["l_len"] = int(z["l_len"])
+    iq = [np.ascontiguousarray(post[a]) for a in range(post.shape[0])]
+    return z, iq, pk, np.ascontiguousarray(z["chan"].reshape(1, 64))
+
+
+@pytest.mark.parametrize("name", ["fixture_siso.npz", "fixture_mimo.npz"])
+def test_reference_fixtures(rx, name):
+    """tools/sig80211GenMultiple{Siso_1x1_0,Mimo_2x2_*}.bin -> the 94-byte frame of tools/debug.txt:5."""
+    z, iq, pk, chan = golden_inputs(name)
+    res = rx.rx(iq, pk, chan, want_llr=True)
+    d = res.desc[0]
+    assert [int(d[k]) for k in ("format", "mcs", "len", "cr", "ampdu", "trellis", "total")] == list(z["tags"])
+    assert np.array_equal(res.packet_llr(0), z["llr"])
+    msgs = res.messages()
+    assert len(msgs) == 1 and msgs[0] == z["msg"].tobytes()
+    assert msgs[0][3:-1] == np.load(os.path.join(GOLD, "frame94.npy")).tobytes()
+
+
+MIMO = [(g.F_HT, 8 + m, 2, 90 + 61 * m, False) for m in range(8)] + [(g.F_VHT, m, 2, 120 + 75 * m, False) for m in range(9)] \
+    + [(g.F_HT, 15, 2, 800, True), (g.F_VHT, 8, 2, 700, True)]
+
+
+@pytest.mark.parametrize("fmt,mcs,nss,length,sgi", MIMO)
+def test_mimo_2x2_all_mcs(refgr, rx, fmt, mcs, nss, length, sgi):
+    b = gp.gen_batch(fmt, mcs % 8 + 8 if fmt == g.F_HT else mcs, nss, length, 4, snr_db=32, short_gi=sgi, seed=300 + mcs)
+    res, msgs = compare_with_reference(refgr, rx, [b])
+    assert len(msgs) == 4
+
+
+def test_mimo_flat_channel_and_siso_packets_on_two_antennas(refgr, rx):
+    """demod2 also takes legacy and 1-SS packets (antenna 1 only) and a mixing channel."""
+    h = np.array([[1.0, 0.35 - 0.2j], [0.25 + 0.3j, 0.9 - 0.1j]])
+    bs = [gp.gen_batch(g.F_HT, 15, 2, 4095, 2, snr_db=35, seed=11, chan=h),
+          gp.gen_batch(g.F_VHT, 5, 2, 600, 2, snr_db=35, seed=12, chan=h),
+          gp.gen_batch(g.F_L, 4, 1, 200, 2, snr_db=30, seed=13, nrx=2, chan=h[:, :1]),
+          gp.gen_batch(g.F_HT, 5, 1, 300, 2, snr_db=30, seed=14, nrx=2, chan=h[:, :1]),
+          gp.gen_batch(g.F_VHT, 6, 1, 300, 2, snr_db=30, seed=15, nrx=2, chan=h[:, :1])]
+    res, msgs = compare_with_reference(refgr, rx, bs)
+    assert len(msgs) == 10
+
+
+def test_drop_gates_and_bad_fcs(refgr, rx):
+    """Corrupted SIG, L-SIG duration too short, wrong FCS: the same packets reach the demod loop and the
+    same (none) are published; good packets around them are unaffected."""
+    bs = [gp.gen_batch(g.F_HT, 3, 1, 300, 2, snr_db=30, seed=20),
+          gp.gen_batch(g.F_HT, 3, 1, 300, 2, snr_db=30, seed=21, corrupt_sig=True),
+          gp.gen_batch(g.F_VHT, 3, 1, 300, 2, snr_db=30, seed=22, l_len_short=3),
+          gp.gen_batch(g.F_HT, 4, 1, 300, 2, snr_db=30, seed=23, l_len_short=2),
+          gp.gen_batch(g.F_VHT, 4, 1, 300, 2, snr_db=30, seed=24, corrupt_fcs=True),
+          gp.gen_batch(g.F_L, 6, 1, 300, 2, snr_db=30, seed=25, corrupt_fcs=True),
+          gp.gen_batch(g.F_L, 3, 1, 77, 2, snr_db=30, seed=26)]
+    res, msgs = compare_with_reference(refgr, rx, bs)
+    assert len(msgs) == 4
+    st = [int(x) for x in res.desc["status"]]
+    assert st[4:8] == [host.ST_DROP_GATE] * 4
+    assert res.n_mpdu - res.n_crc_ok == 6  # corrupted SIG (decoded as legacy garbage) + wrong FCS
+
+
+def test_low_snr_fail_set_matches(refgr, rx):
+    """At an SNR where some packets fail the FCS, the set of published packets is the reference's."""
+    bs = [gp.gen_batch(g.F_HT, 7, 1, 600, 24, snr_db=19.0, seed=31), gp.gen_batch(g.F_VHT, 8, 1, 600, 24, snr_db=24.5, seed=32)]
+    res, msgs = compare_with_reference(refgr, rx, bs)
+    assert 0 < len(msgs) < 48
+
+
+def test_ragged_batch_many_lengths(refgr, rx):
+    """Packets of every code rate and many lengths in one batch (groups are ragged, tails of every phase)."""
+    rng = np.random.default_rng(5)
+    bs = []
+    for i in range(24):
+        fmt = int(rng.integers(0, 3))
+        mcs = int(rng.integers(0, 8 if fmt != g.F_VHT else 9))
+        ln = int(rng.integers(30, 900))
+        bs.append(gp.gen_batch(fmt, mcs, 1, ln, 2, snr_db=30, seed=400 + i))
+    res, msgs = compare_with_reference(refgr, rx, bs)
+    assert len(msgs) == 48
+
+
+def test_empty_batch(rx):
+    res = rx.rx([np.zeros(16, np.complex64)], np.zeros(0, host.PKT_IN_DTYPE), np.zeros((0, 64), np.complex64))
+    assert res.n_mpdu == 0 and res.messages() == []
+
+
+def test_bad_descriptor_is_flagged_not_crashing(rx):
+    b = gp.gen_batch(g.F_L, 3, 1, 100, 2, snr_db=30, seed=40)
+    iq, pk, chan = host.pack_batch([b])
+    pk["iq_offset"][1] = 10 ** 9  # outside the sample array
+    res = rx.rx(iq, pk, chan)
+    assert int(res.desc["status"][1]) == host.ST_BAD_INPUT and len(res.messages()) == 1
+
+
+def test_vht_ampdu_several_subframes(refgr, rx):
+    """A-MPDU with three subframes (and a zero-length delimiter in between): the delimiter walk of
+    decode_impl.cc:336-426 including its length-accumulation quirk."""
+    rng = np.random.default_rng(9)
+    mp = [g.make_mpdus(1, n, rng)[0] for n in (64, 68, 200)]
+    parts = []
+    for i, m in enumerate(mp):
+        a = g.vht_ampdu(m[None, :])[0].copy()
+        if i < len(mp) - 1:
+            a[0] &= 0xFE  # EOF only on the last subframe
+        parts.append(a)
+    psdu = np.concatenate(parts)
+    length = len(psdu) - 4  # gen_batch wraps `mpdus` in one more delimiter; feed the body as the MPDU instead
+    body = psdu[4:][None, :]
+    # first delimiter is rebuilt by vht_ampdu for a length-`length` MPDU: replace it after generation is not possible,
+    # so build the batch from a hand-made PSDU through the lower-level entry
+    b = gp.gen_batch(g.F_VHT, 4, 1, length, 1, snr_db=30, seed=50, mpdus=body)
+    res, msgs = compare_with_reference(refgr, rx, [b])
+    assert res.n_mpdu >= 1
+
+
+def test_split_entry_points_equal_fused(refgr, rx):
+    """w80211_demod_batch output feeds w80211_decode_batch (what the two GR blocks do) == fused path;
+    decode also accepts the REFERENCE demod's LLR stream."""
+    bs = [gp.gen_batch(g.F_L, 7, 1, 1500, 3, snr_db=30, seed=60), gp.gen_batch(g.F_VHT, 7, 1, 900, 3, snr_db=30, seed=61),
+          gp.gen_batch(g.F_HT, 5, 1, 123, 3, snr_db=30, seed=62)]
+    iq, pk, chan = host.pack_batch(bs)
+    fused = rx.rx(iq, pk, chan)
+    dm = rx.demod(iq, pk, chan)
+    dec = rx.decode(dm.desc, dm.llr[: dm.n_llr])
+    assert dec.messages() == fused.messages() and len(fused.messages()) == 9
+    ref_pkts, ref_msgs = ref_chain(refgr, bs)
+    desc = np.zeros(len(ref_pkts), host.DESC_DTYPE)
+    off = 0
+    for i, r in enumerate(ref_pkts):
+        for k in ("format", "mcs", "len", "cr", "ampdu", "trellis", "total"):
+            desc[k][i] = r[k]
+        desc["llr_off"][i] = off + 3 * i  # deliberately unaligned offsets
+        off += r["total"]
+    llr = np.zeros(off + 3 * len(ref_pkts) + 8, np.float32)
+    for i, r in enumerate(ref_pkts):
+        llr[desc["llr_off"][i]: desc["llr_off"][i] + r["total"]] = r["llr"]
+    dec2 = rx.decode(desc, llr)
+    assert dec2.messages() == ref_msgs
+
+
+def test_full_size_batch_properties(rx):
+    """BASELINE-size packets in a batch large enough to fill many groups: every packet must come back
+    with its own bytes (round trip), the FCS residue must hold, and results must not depend on the slot order."""
+    bs = [gp.gen_batch(g.F_VHT, 8, 1, 4088, 96, snr_db=30, seed=70), gp.gen_batch(g.F_HT, 7, 1, 4095, 64, snr_db=30, short_gi=True, seed=71),
+          gp.gen_batch(g.F_L, 7, 1, 1500, 200, snr_db=30, seed=72)]
+    iq, pk, chan = host.pack_batch(bs)
+    res = rx.rx(iq, pk, chan)
+    sent = [m.tobytes() for b in bs for m in b["mpdu"]]
+    got = res.messages()
+    assert [m[3:-1] for m in got] == sent
+    assert all(zlib.crc32(m[3:-1]) == 558161692 for m in got)
+    perm = np.random.default_rng(1).permutation(len(pk))
+    res2 = rx.rx(iq, pk[perm], chan[perm])
+    assert [m[3:-1] for m in res2.messages()] == [sent[i] for i in perm]
