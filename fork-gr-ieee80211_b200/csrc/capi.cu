@@ -52,6 +52,7 @@ struct Slot {
     PinBuf h_desc, h_plan, h_mpdus, h_counters;
     /* batch in flight */
     int npkt = 0, nant = 1, ngroups = 0, ndec = 0, nsymtot = 0;
+    int cr_first[5] = {0, 0, 0, 0, 0};
     bool did_demod = false, did_decode = false, in_host = true;
     uint64_t n_llr = 0, n_bytes = 0, trellis_steps = 0;
     uint32_t mpdu_cap = 0;
@@ -166,7 +167,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
         } else if (assign_llr) {
             d.llr_off = -1;
         }
-        symprefix[p + 1] = symprefix[p] + nsym;
+        symprefix[p + 1] = symprefix[p] + (nsym + 7) / 8; /* demod work items: chunks of DEMOD_SPC = 8 symbols */
     }
     if (assign_llr) s.n_llr = off;
     s.nsymtot = symprefix[npkt];
@@ -195,6 +196,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     std::vector<int4> grp;
     s.h_psdu_off.assign(npkt, 0);
     uint64_t row = 0, wrow = 0, boff = 0;
+    for (int c = 0; c <= 4; c++) s.cr_first[c] = 0;
     for (size_t i = 0; i < dec.size();) {
         int cr = hd[dec[i]].cr;
         int maxT = hd[dec[i]].trellis;
@@ -209,6 +211,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
             slot_pkt.push_back(dec[i]);
         }
         for (; k < 32; k++) slot_pkt.push_back(-1);
+        for (int c = cr + 1; c <= 4; c++) s.cr_first[c] = (int)grp.size() + 1;
         grp.push_back(G);
         row += (uint64_t)G.y;
         wrow += (uint64_t)((maxT + 31) >> 5);
@@ -268,8 +271,8 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
 {
     cudaStream_t st = s.stream;
     w80211_batch_out* out = s.out;
-    w_launch_viterbi(st, s.ngroups, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
-                     (const float*)s.llr.p, (uint2*)s.surv.p);
+    int nvit = w_launch_viterbi(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
+                                (const float*)s.llr.p, (uint2*)s.surv.p);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_VIT], st));
     w_launch_traceback(st, s.ngroups, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
@@ -288,7 +291,7 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
                   (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_POST], st));
-    if (s.ngroups > 0) s.launches += 3;
+    if (s.ngroups > 0) s.launches += 2 + nvit;
     /* results */
     CK(cudaMemcpyAsync(s.h_counters.p, s.counters.p, 64, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(s.h_mpdus.p, s.mpdus.p, (size_t)internal_cap * sizeof(w80211_mpdu), cudaMemcpyDeviceToHost, st));

@@ -141,8 +141,8 @@ void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nan
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nsymtot, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* sym_prefix,
                     const float2* chan, int chan_stride, float* llr);
-void w_launch_viterbi(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
-                      const float* llr, uint2* surv);
+int w_launch_viterbi(cudaStream_t st, const int* cr_first, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
+                     const float* llr, uint2* surv);
 void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
                         const uint2* surv, uint32_t* bits);
 void w_launch_post(cudaStream_t st, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,

@@ -22,6 +22,15 @@
  */
 #include "common.cuh"
 
+#ifndef VIT_MINBLK
+#define VIT_MINBLK 16
+#endif
+#ifndef VIT_INPLACE
+#define VIT_INPLACE 1
+#endif
+#ifndef VIT_PF
+#define VIT_PF 8 /* L1 prefetch distance, in bodies */
+#endif
 #define MASK_FULL 0 /* both LLRs present */
 #define MASK_A 1    /* only A (t0) present, t1 = 0 */
 #define MASK_B 2    /* only B (t1) present, t0 = 0 */
@@ -99,6 +108,103 @@ __device__ __forceinline__ void body(float (&m)[64], float (&n)[64], const float
     }
 }
 
+/* ---- in-place variant.  A butterfly reads states (2b, 2b+1) and writes states (b, b+32); writing the
+ * results back into the two registers just read turns the state <-> register map into a 6-bit
+ * rotation per step, identity again after 6 steps.  Six steps are unrolled with the map as a
+ * compile-time constant, so only 64 metric registers are live (no second array). */
+__host__ __device__ constexpr int rol6(int x, int k) { return ((x << k) | (x >> (6 - k))) & 63; }
+
+template <int PH, int MASK>
+__device__ __forceinline__ void acs_ip(float (&m)[64], float t0, float t1, uint32_t& lo, uint32_t& hi)
+{
+    const float t3 = MASK == MASK_FULL ? __fadd_rn(t1, t0) : 0.0f;
+    lo = 0;
+    hi = 0;
+#pragma unroll
+    for (int b = 31; b >= 0; b--) {
+        const int L = w_branch_label(2 * b, 0);
+        const int p = rol6(2 * b, PH), q = rol6(2 * b + 1, PH);
+        const float ma = m[p], mb = m[q];
+        float c0 = add_label<MASK>(ma, L, t0, t1, t3);
+        float c1 = add_label<MASK>(mb, 3 - L, t0, t1, t3);
+        float e0 = add_label<MASK>(ma, 3 - L, t0, t1, t3);
+        float e1 = add_label<MASK>(mb, L, t0, t1, t3);
+        m[p] = fmaxf(c0, c1);
+        lo = __funnelshift_l(__float_as_uint(__fsub_rn(c0, c1)), lo, 1);
+        m[q] = fmaxf(e0, e1);
+        hi = __funnelshift_l(__float_as_uint(__fsub_rn(e0, e1)), hi, 1);
+    }
+}
+
+template <int PH, int M0, int M1>
+__device__ __forceinline__ void acs2_ip(float (&m)[64], float a0, float a1, float b0, float b1, uint4* dst)
+{
+    uint4 w;
+    acs_ip<PH, M0>(m, a0, a1, w.x, w.y);
+    acs_ip<PH + 1, M1>(m, b0, b1, w.z, w.w);
+    *dst = w;
+}
+
+/* six steps, rates 1/2 (12 LLRs) and 3/4 (8 LLRs) */
+template <int CR>
+__device__ __forceinline__ void body6(float (&m)[64], const float4* v, uint4* dst)
+{
+    if (CR == W80211_CR_12) {
+        acs2_ip<0, MASK_FULL, MASK_FULL>(m, v[0].x, v[0].y, v[0].z, v[0].w, dst);
+        acs2_ip<2, MASK_FULL, MASK_FULL>(m, v[1].x, v[1].y, v[1].z, v[1].w, dst + 32);
+        acs2_ip<4, MASK_FULL, MASK_FULL>(m, v[2].x, v[2].y, v[2].z, v[2].w, dst + 64);
+    } else {
+        acs2_ip<0, MASK_FULL, MASK_A>(m, v[0].x, v[0].y, v[0].z, 0.f, dst);
+        acs2_ip<2, MASK_B, MASK_FULL>(m, 0.f, v[0].w, v[1].x, v[1].y, dst + 32);
+        acs2_ip<4, MASK_A, MASK_B>(m, v[1].z, 0.f, 0.f, v[1].w, dst + 64);
+    }
+}
+
+template <int PH>
+__device__ __forceinline__ void tail_ip(float (&m)[64], int& t, int trellis, int& ph, int period, const float*& q, uint2* surv2)
+{
+    if (t < trellis) {
+        bool hasA = ph == 0 || (ph & 1), hasB = ph == 0 || !(ph & 1);
+        float t0 = 0.0f, t1 = 0.0f;
+        if (hasA) t0 = __ldg(q++);
+        if (hasB) t1 = __ldg(q++);
+        uint2 w;
+        acs_ip<PH, MASK_FULL>(m, t0, t1, w.x, w.y);
+        surv2[((size_t)(t >> 1) * 32) * 2 + (t & 1)] = w;
+        if (++ph >= period) ph = 0;
+        t++;
+    }
+}
+
+template <int CR>
+__device__ __forceinline__ void viterbi_run6(const float* __restrict__ llr, int trellis, uint4* __restrict__ surv4)
+{
+    enum { NV = CR == W80211_CR_12 ? 3 : 2 };
+    const float NEG = -1000000000000000.0f;
+    float m[64];
+#pragma unroll
+    for (int i = 0; i < 64; i++) m[i] = NEG;
+    m[0] = 0.0f;
+    const int nbody = trellis / 6;
+    const float4* src = reinterpret_cast<const float4*>(llr);
+    for (int b = 0; b < nbody; b++) {
+        float4 cur[NV];
+#pragma unroll
+        for (int k = 0; k < NV; k++) cur[k] = __ldg(src + (size_t)b * NV + k);
+        if (b + VIT_PF < nbody) asm volatile("prefetch.global.L1 [%0];" ::"l"(src + (size_t)(b + VIT_PF) * NV));
+        body6<CR>(m, cur, surv4 + (size_t)b * 3 * 32);
+    }
+    int t = nbody * 6, ph = 0;
+    const int period = CR == W80211_CR_12 ? 1 : 3;
+    const float* q = llr + (size_t)nbody * NV * 4;
+    uint2* surv2 = reinterpret_cast<uint2*>(surv4);
+    tail_ip<0>(m, t, trellis, ph, period, q, surv2);
+    tail_ip<1>(m, t, trellis, ph, period, q, surv2);
+    tail_ip<2>(m, t, trellis, ph, period, q, surv2);
+    tail_ip<3>(m, t, trellis, ph, period, q, surv2);
+    tail_ip<4>(m, t, trellis, ph, period, q, surv2);
+}
+
 /* grp[g] = {x: first survivor row (even), y: rows reserved (even, >= max trellis in the group),
  *           z: first bit-word row, w: code rate of the group} */
 template <int CR>
@@ -151,23 +257,25 @@ __device__ __forceinline__ void viterbi_run(const float* __restrict__ llr, int t
     }
 }
 
-__global__ void __launch_bounds__(32, 16) viterbi_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
-                                                         const w80211_desc* __restrict__ desc, const float* __restrict__ llr,
-                                                         uint2* __restrict__ surv)
+/* one kernel per code rate (groups are sorted by rate), so each gets its own register allocation */
+template <int CR>
+__global__ void __launch_bounds__(32, VIT_MINBLK) viterbi_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
+                                                                 const w80211_desc* __restrict__ desc, const float* __restrict__ llr,
+                                                                 uint2* __restrict__ surv, int g0)
 {
-    const int g = blockIdx.x, lane = threadIdx.x;
+    const int g = g0 + blockIdx.x, lane = threadIdx.x;
     const int4 G = grp[g];
     const int pkt = slot_pkt[g * 32 + lane];
     if (pkt < 0) return;
     const int trellis = desc[pkt].trellis;
     const float* l = llr + desc[pkt].llr_off;
     uint4* s4 = reinterpret_cast<uint4*>(surv + (size_t)G.x * 32) + lane;
-    switch (G.w) {
-    case W80211_CR_12: viterbi_run<W80211_CR_12>(l, trellis, s4); break;
-    case W80211_CR_23: viterbi_run<W80211_CR_23>(l, trellis, s4); break;
-    case W80211_CR_34: viterbi_run<W80211_CR_34>(l, trellis, s4); break;
-    default: viterbi_run<W80211_CR_56>(l, trellis, s4); break;
-    }
+#if VIT_INPLACE
+    if (CR == W80211_CR_12 || CR == W80211_CR_34)
+        viterbi_run6<CR>(l, trellis, s4);
+    else
+#endif
+        viterbi_run<CR>(l, trellis, s4);
 }
 
 /* vstb_end (decode_impl.cc:282-302): traceback from state 0 at the end of the trellis.  One thread
@@ -211,11 +319,22 @@ __global__ void __launch_bounds__(32) traceback_kernel(const int4* __restrict__ 
     }
 }
 
-void w_launch_viterbi(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
-                      const float* llr, uint2* surv)
+int w_launch_viterbi(cudaStream_t st, const int* cr_first /* [5]: first group of each code rate, [4] = ngroups */, const int4* grp,
+                     const int* slot_pkt, const w80211_desc* desc, const float* llr, uint2* surv)
 {
-    if (ngroups <= 0) return;
-    viterbi_kernel<<<ngroups, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv);
+    int launches = 0;
+    for (int cr = 0; cr < 4; cr++) {
+        int n = cr_first[cr + 1] - cr_first[cr];
+        if (n <= 0) continue;
+        launches++;
+        switch (cr) {
+        case W80211_CR_12: viterbi_kernel<W80211_CR_12><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
+        case W80211_CR_23: viterbi_kernel<W80211_CR_23><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
+        case W80211_CR_34: viterbi_kernel<W80211_CR_34><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
+        default: viterbi_kernel<W80211_CR_56><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
+        }
+    }
+    return launches;
 }
 
 void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
