@@ -118,33 +118,38 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.rows.append([x.strip() for x in ln.split(",")])
+            self.rows.append([time.time()] + [x.strip() for x in ln.split(",")])
 
-    def stop(self):
+    def mark(self):
+        return time.time()
+
+    def stop(self, t_from=None, t_to=None):
+        """Samples that arrived inside [t_from, t_to] (the timed region); all of them when no window is given."""
         if self.proc:
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=2)
             except Exception:
                 pass
-        sm = [float(r[0]) for r in self.rows if len(r) >= 8 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        rows = [r[1:] for r in self.rows if len(r) >= 9 and (t_from is None or t_from <= r[0] <= t_to + 0.15)]
+        sm = [float(r[0]) for r in rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
+        pw = [float(r[2]) for r in rows if r[2].replace(".", "").isdigit()]
         reasons = set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            if len(r) >= 8:
-                for i, nm in enumerate(names):
-                    if r[4 + i].lower().startswith("active"):
-                        reasons.add(nm)
+        for r in rows:
+            for i, nm in enumerate(names):
+                if r[4 + i].lower().startswith("active"):
+                    reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "power_w": float(np.median(pw)) if pw else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
 # ------------------------------------------------------------------ our arm
@@ -165,7 +170,10 @@ def main_gpu(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    P = args.packets
+    nsm = torch.cuda.get_device_properties(local).multi_processor_count
+    # two full waves of the Viterbi kernel: 12 one-warp blocks per SM, one packet per lane
+    P = args.packets if args.packets > 0 else nsm * 12 * 32 * 2
+    PE = min(P, args.e2e_packets if args.e2e_packets > 0 else nsm * 12 * 32 // 2)  # host-fed leg: PCIe-bound, smaller batches
     # ---- synthetic batch: N_UNIQUE distinct packets (own seed per rank), tiled to P packets per step
     ub = gen_unique(N_UNIQUE, 4 + 17 * rank)
     iq_u, pk_u, ch_u = host.pack_batch([ub])
@@ -178,19 +186,19 @@ def main_gpu(args):
     pk["l_len"] = pk_u["l_len"][0]
     chan = np.ascontiguousarray(np.tile(ch_u, (reps, 1))[:P])
     # host copy (pinned) for the end-to-end leg, device copy for the resident leg
-    iq_host = torch.empty(P * nsamp, dtype=torch.complex64).pin_memory()
-    src = torch.from_numpy(iq_u[0])
+    iq_dev = torch.empty(P * nsamp, dtype=torch.complex64, device=dev)
+    src = torch.from_numpy(iq_u[0]).to(dev)
     for r in range(reps):
         n = min(N_UNIQUE, P - r * N_UNIQUE) * nsamp
-        iq_host[r * N_UNIQUE * nsamp: r * N_UNIQUE * nsamp + n] = src[:n]
-    pk_host = torch.from_numpy(pk.view(np.uint8).copy()).pin_memory()
-    ch_host = torch.from_numpy(chan.view(np.float32).reshape(-1).copy()).pin_memory()
-    iq_dev = iq_host.to(dev)
-    pk_dev = pk_host.to(dev)
-    ch_dev = ch_host.to(dev)
+        iq_dev[r * N_UNIQUE * nsamp: r * N_UNIQUE * nsamp + n] = src[:n]
+    pk_dev = torch.from_numpy(pk.view(np.uint8).copy()).to(dev)
+    ch_dev = torch.from_numpy(chan.view(np.float32).reshape(-1).copy()).to(dev)
+    iq_host = iq_dev[:PE * nsamp].cpu().pin_memory()
+    pk_host = torch.from_numpy(pk[:PE].view(np.uint8).copy()).pin_memory()
+    ch_host = torch.from_numpy(chan[:PE].view(np.float32).reshape(-1).copy()).pin_memory()
 
     rx = host.Receiver(local, nslots=2)
-    bytes_cap = P * 4160 + 4096
+    bytes_cap = P * (MPDU_LEN + 72) + 4096
     mp_cap = 2 * P + 64
 
     def dev_out():
@@ -204,23 +212,25 @@ def main_gpu(args):
         bo.psdu_off, bo.mpdus, bo.mpdu_capacity = t["psdu_off"].data_ptr(), t["mpdus"].data_ptr(), mp_cap
         return bo, t
 
+    bytes_cap_e, mp_cap_e = PE * (MPDU_LEN + 72) + 4096, 2 * PE + 64
+
     def host_out():
-        t = {"desc": torch.empty(P * host.DESC_DTYPE.itemsize, dtype=torch.uint8).pin_memory(),
-             "bytes": torch.empty(bytes_cap, dtype=torch.uint8).pin_memory(),
-             "psdu_off": torch.empty(P, dtype=torch.int32).pin_memory(),
-             "mpdus": torch.empty(mp_cap * 16, dtype=torch.uint8).pin_memory()}
+        t = {"desc": torch.empty(PE * host.DESC_DTYPE.itemsize, dtype=torch.uint8).pin_memory(),
+             "bytes": torch.empty(bytes_cap_e, dtype=torch.uint8).pin_memory(),
+             "psdu_off": torch.empty(PE, dtype=torch.int32).pin_memory(),
+             "mpdus": torch.empty(mp_cap_e * 16, dtype=torch.uint8).pin_memory()}
         bo = host.BatchOut()
         bo.mem = host.MEM_HOST
-        bo.desc, bo.bytes, bo.bytes_capacity = t["desc"].data_ptr(), t["bytes"].data_ptr(), bytes_cap
-        bo.psdu_off, bo.mpdus, bo.mpdu_capacity = t["psdu_off"].data_ptr(), t["mpdus"].data_ptr(), mp_cap
+        bo.desc, bo.bytes, bo.bytes_cap_eacity = t["desc"].data_ptr(), t["bytes"].data_ptr(), bytes_cap_e
+        bo.psdu_off, bo.mpdus, bo.mpdu_capacity = t["psdu_off"].data_ptr(), t["mpdus"].data_ptr(), mp_cap_e
         return bo, t
 
     bi_dev = host.Receiver.make_in([iq_dev.data_ptr()], pk_dev.data_ptr(), ch_dev.data_ptr(), mem=host.MEM_DEVICE,
                                    nsamples=P * nsamp, npkt=P)
     bi_host = host.Receiver.make_in([iq_host.data_ptr()], pk_host.data_ptr(), ch_host.data_ptr(), mem=host.MEM_DEVICE,
-                                    nsamples=P * nsamp, npkt=P)
+                                    nsamples=PE * nsamp, npkt=PE)
     bi_host.mem = host.MEM_HOST
-    bo_dev, keep_dev = dev_out()
+    bo_d = [dev_out() for _ in range(2)]
     bo_h = [host_out() for _ in range(2)]
     L, h = rx.L, rx.h
 
@@ -229,63 +239,70 @@ def main_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step_resident():
-        rx._check(L.w80211_rx_submit(h, 0, C.byref(bi_dev), C.byref(bo_dev)))
-        rx._check(L.w80211_rx_collect(h, 0))
-        return bo_dev.psdu_bits_ok, bo_dev.n_crc_ok
+    stage = {k: 0.0 for k in ("header", "demod", "viterbi", "traceback", "post", "total")}
+    counters = {"launches": 0}
 
-    # ---- resident leg: W warm-up + K timed steps, sequential on slot 0 (clean per-stage events)
-    for _ in range(args.warmup):
-        step_resident()
+    def run_steps(nsteps, bi, bos, tally, depth=2):
+        """nsteps batches through w80211_rx_submit / collect with two slots in flight: the host plans batch i+1
+        (it needs the header kernel's descriptors) while the GPU decodes batch i."""
+        tot_bits = tot_ok = 0
+        pend = []
+
+        def collect(ps):
+            nonlocal tot_bits, tot_ok
+            rx._check(L.w80211_rx_collect(h, ps))
+            tot_bits += bos[ps][0].psdu_bits_ok
+            tot_ok += bos[ps][0].n_crc_ok
+            if tally:
+                t = rx.timing(ps)
+                counters["launches"] += t.launches
+                for k in stage:
+                    stage[k] += getattr(t, k)
+
+        for i in range(nsteps):
+            s = i & 1
+            if len(pend) == depth:
+                collect(pend.pop(0))
+            rx._check(L.w80211_rx_submit(h, s, C.byref(bi), C.byref(bos[s][0])))
+            pend.append(s)
+        for ps in pend:
+            collect(ps)
+        return tot_bits, tot_ok
+
+    # ---- resident leg: inputs already in HBM, results left in HBM
     clocks = ClockSampler(local)
     clocks.start()
+    run_steps(max(args.warmup, 3), bi_dev, bo_d, False)
     barrier()
+    t_from = clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    bits = npk_ok = launches = 0
-    stage = {k: 0.0 for k in ("header", "demod", "viterbi", "traceback", "post", "total")}
-    for _ in range(args.steps):
-        b, n = step_resident()
-        bits += b
-        npk_ok += n
-        t = rx.timing(0)
-        launches += t.launches
-        for k in stage:
-            stage[k] += getattr(t, k)
+    bits, npk_ok = run_steps(args.steps, bi_dev, bo_d, False)
     barrier()
     e1.record()
     e1.synchronize()
     ms = e0.elapsed_time(e1)
-    clk = clocks.stop()
+    # per-kernel durations (CUDA events on the slot's own stream): the same steps once more with ONE slot in
+    # flight, because with two streams the events of one slot also span the other slot's kernels
+    KSEQ = min(args.steps, 5)
+    run_steps(KSEQ, bi_dev, bo_d, True, depth=1)
+    torch.cuda.synchronize()
+    t_to = clocks.mark()
+    launches = counters["launches"] * args.steps // KSEQ
 
-    # ---- end-to-end leg: host buffers -> C ABI -> host results, two slots in flight
-    def e2e_run(nsteps):
-        tot = 0
-        pend = []
-        for i in range(nsteps):
-            s = i & 1
-            if len(pend) == 2:
-                ps = pend.pop(0)
-                rx._check(L.w80211_rx_collect(h, ps))
-                tot += bo_h[ps][0].psdu_bits_ok
-            rx._check(L.w80211_rx_submit(h, s, C.byref(bi_host), C.byref(bo_h[s][0])))
-            pend.append(s)
-        for ps in pend:
-            rx._check(L.w80211_rx_collect(h, ps))
-            tot += bo_h[ps][0].psdu_bits_ok
-        return tot
-
-    e2e_run(max(2, min(args.warmup, 3)))
+    # ---- end-to-end leg: pinned host buffers -> C ABI -> pinned host results, two slots in flight
+    run_steps(2, bi_host, bo_h, False)
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    e2e_bits = e2e_run(args.steps)
+    e2e_bits, _ = run_steps(args.steps, bi_host, bo_h, False)
     barrier()
     f1.record()
     f1.synchronize()
     e2e_ms = f0.elapsed_time(f1)
-    h2d = P * nsamp * 8 + pk_host.numel() + ch_host.numel() * 4
-    d2h = int(bo_h[0][0].n_bytes) + int(bo_h[0][0].n_mpdu) * 16 + 64 + P * host.DESC_DTYPE.itemsize
+    clk = clocks.stop(t_from, t_to)
+    h2d = PE * nsamp * 8 + pk_host.numel() + ch_host.numel() * 4
+    d2h = int(bo_h[0][0].n_bytes) + int(bo_h[0][0].n_mpdu) * 16 + 64 + PE * host.DESC_DTYPE.itemsize
 
     # ---- max over ranks, totals over ranks
     vals = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
@@ -308,37 +325,49 @@ def main_gpu(args):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s"
-    # dominant kernel: the Viterbi forward pass.  Algorithmic bytes per trellis step: LLRs read
+    # per-packet sizes from the descriptor the header stage produced (C4: trellis 32760, total 43680, nSym 105, nCBPS 416)
+    d0 = np.frombuffer(bo_h[0][1]["desc"].numpy(), host.DESC_DTYPE)[0]
+    trellis, total, nsym, ncbps, nsymsamp = (int(d0[k]) for k in ("trellis", "total", "nsym", "ncbps", "nsymsamp"))
+    # dominant kernel: the Viterbi forward pass.  Algorithmic bytes per trellis step (SURVEY.md 8(d)): LLRs read
     # (total*4/trellis = 5.33 B at rate 3/4) + one 64-bit survivor word written.
-    st = rx.stats()
-    steps_per_launch = 32760.0 * P
-    vit_ms = stage["viterbi"] / K
-    alg_bytes = steps_per_launch * (43680.0 * 4 / 32760.0 + 8.0)
+    steps_per_launch = float(trellis) * P
+    vit_ms = stage["viterbi"] / KSEQ
+    alg_bytes = steps_per_launch * (total * 4.0 / trellis + 8.0)
     achieved = alg_bytes / (vit_ms * 1e-3) / 1e9
     sm_clk = clk["sm_mhz"] or float(peaks.get("sm_max_mhz", 1965.0))
     acs_per_s = steps_per_launch * 64 / (vit_ms * 1e-3)
-    acs_peak = 148 * 128 * sm_clk * 1e6 / 3.0
-    demod_ms = stage["demod"] / K
-    demod_bytes = P * 105.0 * (80 * 8 + 416 * 4)
+    acs_peak = nsm * 128 * sm_clk * 1e6 / 3.0
+    alu_peak = nsm * 4 * 32 * sm_clk * 1e6 / 4.0  # per ACS: FMNMX + SHF on the ALU pipe, 2 cycles each per warp and SMSP (profiles/r1_pipebench.txt)
+    demod_ms = stage["demod"] / KSEQ
+    demod_bytes = float(P) * nsym * (nsymsamp * 8 + ncbps * 4)
+    tb_ms = stage["traceback"] / KSEQ
+    tb_bytes = steps_per_launch * 8.0 + steps_per_launch / 8.0
     line = {
         "metric": METRIC, "value": bits / (ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "packets_per_step_per_gpu": P, "unique_packets": N_UNIQUE,
+        "config": {"workload": WORKLOAD if MPDU_LEN == 4088 else "PROFILING VARIANT, MPDU %d B, not the benchmark workload" % MPDU_LEN,
+                   "packets_per_step_per_gpu": P, "unique_packets": N_UNIQUE, "slots_in_flight": 2,
                    "l2": "inputs larger than L2 (%.1f GB of IQ per step)" % (P * nsamp * 8 / 1e9), "parallelism": "packets sharded by rank, no collective"},
         "packets_per_s": npk_ok / (ms * 1e-3), "fcs_ok_per_step": npk_ok / K / world,
         "e2e": {"value": e2e_bits / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": e2e_ms / K, "note": "pinned host buffers through w80211_rx_submit/collect, 2 slots in flight"},
+                "ms_per_step": e2e_ms / K, "packets_per_step_per_gpu": PE,
+                "note": "pinned host buffers through w80211_rx_submit/collect, 2 slots in flight; PCIe-bound, so smaller batches than the resident leg"},
         "gpu_launches": int(launches),
         "clocks": clk,
-        "stage_ms_per_step": {k: v / K for k, v in stage.items()},
+        "stage_ms_per_step": {k: v / KSEQ for k, v in stage.items()},
+        "stage_note": "per-kernel CUDA-event durations from %d steps with one slot in flight, run right after the timed region" % KSEQ,
         "roofline": {"bound": "hbm", "kernel": "viterbi_kernel", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
                      "note": "the kernel is FP32/ALU issue bound, not HBM bound: see roofline_compute"},
         "roofline_compute": {"kernel": "viterbi_kernel", "bound": "fp32+alu issue", "achieved": acs_per_s / 1e12, "peak": acs_peak / 1e12,
                              "unit": "T ACS/s", "frac": acs_per_s / acs_peak,
-                             "peak_def": "148 SMs x 128 lanes x SM clock under load / 3 lane-ops per ACS (SURVEY.md 8(d))", "sm_mhz": sm_clk},
+                             "peak_def": "SMs x 128 lanes x SM clock under load / 3 lane-ops per ACS (SURVEY.md 8(d))", "sm_mhz": sm_clk,
+                             "alu_pipe_peak": alu_peak / 1e12, "alu_pipe_frac": acs_per_s / alu_peak,
+                             "alu_pipe_def": "per ACS one FMNMX and one SHF, both on the half-rate ALU pipe: SMs x 4 SMSPs x 32 lanes x clock / 4 cycles"},
         "roofline_demod": {"kernel": "demod_kernel", "bound": "hbm", "achieved": demod_bytes / (demod_ms * 1e-3) / 1e9, "peak": hbm_peak,
                            "unit": "GB/s", "frac": demod_bytes / (demod_ms * 1e-3) / 1e9 / hbm_peak},
+        "roofline_traceback": {"kernel": "traceback_kernel", "bound": "hbm", "achieved": tb_bytes / (tb_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                               "unit": "GB/s", "frac": tb_bytes / (tb_ms * 1e-3) / 1e9 / hbm_peak},
     }
     # ---- CPU baseline beside it (rank 0, N = 1 only): the reference's own blocks on the host cores
     if world == 1 and not args.no_cpu:
@@ -359,13 +388,18 @@ def main_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--packets", type=int, default=int(os.environ.get("W80211_BENCH_PACKETS", "32768")))
+    ap.add_argument("--packets", type=int, default=int(os.environ.get("W80211_BENCH_PACKETS", "0")),
+                    help="packets per step and GPU (0 = two full waves of the Viterbi kernel: SMs x 12 x 32 x 2)")
+    ap.add_argument("--e2e-packets", type=int, default=0, help="packets per step and GPU of the host-fed leg (0 = SMs x 12 x 32 / 2)")
+    ap.add_argument("--mpdu-len", type=int, default=4088, help="profiling only: shorter packets; the reported workload is the default")
     ap.add_argument("--ref-packets", type=int, default=96, help="packets per core and step for the CPU reference")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    global MPDU_LEN
+    MPDU_LEN = args.mpdu_len
     if args.impl == "reference":
         return main_reference(args)
     return main_gpu(args)

@@ -23,10 +23,13 @@
 #include "common.cuh"
 
 #ifndef VIT_MINBLK
-#define VIT_MINBLK 16
+#define VIT_MINBLK 12 /* one-warp blocks per SM: 12 -> 168 registers, no spills; measured best (profiles/r1_viterbi_sweep.txt) */
 #endif
 #ifndef VIT_INPLACE
 #define VIT_INPLACE 1
+#endif
+#ifndef VIT_REGPF
+#define VIT_REGPF 1 /* 1: software-pipelined register prefetch of the next body's LLRs */
 #endif
 #ifndef VIT_PF
 #define VIT_PF 8 /* L1 prefetch distance, in bodies */
@@ -187,6 +190,21 @@ __device__ __forceinline__ void viterbi_run6(const float* __restrict__ llr, int 
     m[0] = 0.0f;
     const int nbody = trellis / 6;
     const float4* src = reinterpret_cast<const float4*>(llr);
+#if VIT_REGPF
+    /* next body's LLRs are loaded into registers while the current body computes; L2 prefetch further ahead */
+    float4 cur[NV], nxt[NV];
+#pragma unroll
+    for (int k = 0; k < NV; k++) cur[k] = nbody > 0 ? __ldg(src + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int b = 0; b < nbody; b++) {
+        const int bn = b + 1 < nbody ? b + 1 : b;
+#pragma unroll
+        for (int k = 0; k < NV; k++) nxt[k] = __ldg(src + (size_t)bn * NV + k);
+        if (b + VIT_PF < nbody) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(b + VIT_PF) * NV));
+        body6<CR>(m, cur, surv4 + (size_t)b * 3 * 32);
+#pragma unroll
+        for (int k = 0; k < NV; k++) cur[k] = nxt[k];
+    }
+#else
     for (int b = 0; b < nbody; b++) {
         float4 cur[NV];
 #pragma unroll
@@ -194,6 +212,7 @@ __device__ __forceinline__ void viterbi_run6(const float* __restrict__ llr, int 
         if (b + VIT_PF < nbody) asm volatile("prefetch.global.L1 [%0];" ::"l"(src + (size_t)(b + VIT_PF) * NV));
         body6<CR>(m, cur, surv4 + (size_t)b * 3 * 32);
     }
+#endif
     int t = nbody * 6, ph = 0;
     const int period = CR == W80211_CR_12 ? 1 : 3;
     const float* q = llr + (size_t)nbody * NV * 4;
