@@ -578,6 +578,21 @@ void* w80211_stream(const w80211_ctx* ctx, int slot)
     return (void*)ctx->slots[slot].stream;
 }
 
+void* w80211_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void w80211_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
+}
+
 int w80211_rx_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w80211_batch_out* out)
 {
     if (!ctx) return W80211_E_ARG;

@@ -19,7 +19,7 @@ F_L, F_HT, F_VHT = 0, 1, 2
 SYMBOLS = [
     "w80211_abi_version", "w80211_sizeof", "w80211_create", "w80211_destroy", "w80211_last_error", "w80211_stats_get",
     "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
-    "w80211_rx_collect", "w80211_rx_batch",
+    "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free",
 ]
 
 

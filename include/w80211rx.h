@@ -169,6 +169,11 @@ int w80211_timing_get(const w80211_ctx* ctx, int slot, w80211_timing* out);
 /* the CUDA stream (cudaStream_t) slot `slot` launches on, for callers that time with their own events */
 void* w80211_stream(const w80211_ctx* ctx, int slot);
 
+/* Page-locked host memory for staging buffers, so that a caller (the GNU Radio blocks in gr/lib) gets
+ * full-speed DMA without linking the CUDA runtime itself.  NULL when the allocation fails. */
+void* w80211_host_alloc(size_t bytes);
+void w80211_host_free(void* p);
+
 /* IQ -> LLR stream + descriptors: what demod / demod2 write to their output port.
  * out->desc and out->llr are filled; nothing is decoded.  Synchronous. */
 int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out);

@@ -7,6 +7,10 @@
  * Nothing here restates reference arithmetic: it only creates blocks through
  * their public make() factories and plays scheduler (mock_scheduler.h).
  * Test infrastructure / CPU baseline only -- never linked into the product.
+ *
+ * With -DW80211_DRIVER_OURS the same stream / block / scheduler entry points are compiled against
+ * THIS repo's drop-in blocks (gr/include, gr/lib) instead, into oracle/_ours/libours80211.so: the
+ * block-level equivalence tests then feed identical streams to both libraries (tests/test_gr_blocks.py).
  */
 #include <cstdint>
 #include <cstring>
@@ -17,9 +21,11 @@
 #include <gnuradio/ieee80211/decode.h>
 #include <gnuradio/ieee80211/demod.h>
 #include <gnuradio/ieee80211/demod2.h>
+#ifndef W80211_DRIVER_OURS
 #include <gnuradio/ieee80211/signal.h>
 #include <gnuradio/ieee80211/signal2.h>
 #include "cloud80211phy.h"
+#endif
 #include "mock_scheduler.h"
 
 using gr::mock_stream;
@@ -101,11 +107,14 @@ ref_block* ref_block_new(const char* kind, int a0, int a1)
 {
     ref_block* b = new ref_block;
     std::string k(kind);
+#ifndef W80211_DRIVER_OURS
     if (k == "signal")
         b->blk = gr::ieee80211::signal::make();
     else if (k == "signal2")
         b->blk = gr::ieee80211::signal2::make();
-    else if (k == "demod")
+    else
+#endif
+    if (k == "demod")
         b->blk = gr::ieee80211::demod::make(a0, a1);
     else if (k == "demod2")
         b->blk = gr::ieee80211::demod2::make();
@@ -146,6 +155,7 @@ int ref_block_msg_len(const ref_block* b, int i) { return (int)b->msgs[i].size()
 const uint8_t* ref_block_msg_data(const ref_block* b, int i) { return b->msgs[i].data(); }
 void ref_block_clear_msgs(ref_block* b) { b->msgs.clear(); }
 
+#ifndef W80211_DRIVER_OURS
 /* ------------------------------------------- PHY library entry points
  * Thin pass-throughs to free functions of the reference's cloud80211phy.cc,
  * for unit-level parity tests of the restatement and of the CUDA kernels. */
@@ -292,5 +302,7 @@ int ref_check_crc8(const uint8_t* bits42)
     memcpy(tmp, bits42, 42);
     return checkBitCrc8(tmp, 34, &tmp[34]) ? 1 : 0;
 }
+
+#endif /* !W80211_DRIVER_OURS */
 
 } /* extern "C" */

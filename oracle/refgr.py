@@ -19,6 +19,17 @@ def available():
     return os.path.exists(_LIB_PATH)
 
 
+def load_harness(path):
+    """A second copy of this module bound to another library with the same stream / block entry points:
+    oracle/_ours/libours80211.so, this repo's GNU Radio blocks under the same mock scheduler."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("refgr_harness_" + os.path.basename(path).replace(".", "_"), __file__)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod._LIB_PATH = path
+    return mod
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -56,6 +67,9 @@ def lib():
         L.ref_block_msg_data.restype = vp
         L.ref_block_msg_data.argtypes = [vp, ci]
         L.ref_block_clear_msgs.argtypes = [vp]
+        if not hasattr(L, "ref_parse_legacy"):  # the harness build of this repo's own blocks (oracle/_ours) has no PHY entry points
+            _lib = L
+            return _lib
         L.ref_parse_legacy.argtypes = [ci, ci, vp]
         L.ref_parse_ht.argtypes = [vp, vp]
         L.ref_parse_vht.argtypes = [vp, vp, vp]

@@ -1,0 +1,147 @@
+"""Block-level equivalence: this repo's GNU Radio blocks (gr/lib: demod, demod2, decode -- same factories, io
+signatures, tags and messages as the reference's) against the reference's own blocks, both driven by the
+same single-threaded mock scheduler over the same streams (oracle/mock_scheduler.h).
+
+The harness library oracle/_ours/libours80211.so = gr/lib/*.cc + the mock GNU Radio surface, linked to the
+product libw80211rx.so; oracle/_ref/libref80211.so = the reference's sources, unchanged."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import w80211rx
+from util import ref_chain
+
+gp, g, host = w80211rx.gen_ppdu, w80211rx.gen, w80211rx.host
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OURS_PATH = os.path.join(ROOT, "oracle", "_ours", "libours80211.so")
+
+
+@pytest.fixture(scope="module")
+def ours(refgr):
+    assert os.path.exists(OURS_PATH), "oracle/_ours/libours80211.so missing: run __graft_entry__.build() (make -C oracle ours)"
+    return refgr.load_harness(OURS_PATH)
+
+
+def packets_of(batches):
+    pk = []
+    for b in batches:
+        pk += gp.to_packets(b)
+    for i, p in enumerate(pk):
+        p["seq"] = i
+        p["cfo"], p["snr"], p["rssi"] = 0.01 * i - 0.2, 20.0 + i, -50.0 - i
+    return pk
+
+
+def same_llr_stream(a, b):
+    """a, b: Stream objects (possibly of different libraries): same items, same tags on the same items."""
+    da, db = a.data(), b.data()
+    assert da.shape == db.shape, (da.shape, db.shape)
+    assert np.array_equal(da, db), "%d LLRs differ" % int((da != db).sum())
+    ta, tb = a.tags(), b.tags()
+    assert [o for o, _ in ta] == [o for o, _ in tb]
+    for (_, x), (_, y) in zip(ta, tb):
+        assert set(x) == set(y), set(x) ^ set(y)
+        for k in x:
+            if isinstance(x[k], float):
+                assert abs(x[k] - y[k]) <= 1e-3 * max(1.0, abs(y[k])), (k, x[k], y[k])
+            else:
+                assert x[k] == y[k], (k, x[k], y[k])
+
+
+MIX = [(g.F_L, 0, 1, 94, False), (g.F_L, 7, 1, 1500, False), (g.F_HT, 7, 1, 900, True), (g.F_HT, 2, 1, 200, False),
+       (g.F_VHT, 8, 1, 1200, False), (g.F_VHT, 3, 1, 333, True)]
+
+
+def mixed_batches(nant=1, n=3):
+    if nant == 1:
+        return [gp.gen_batch(f, m, s, ln, n, snr_db=30, short_gi=sgi, seed=700 + i) for i, (f, m, s, ln, sgi) in enumerate(MIX)] \
+            + [gp.gen_batch(g.F_HT, 3, 1, 300, 2, snr_db=30, seed=721, corrupt_sig=True),
+               gp.gen_batch(g.F_VHT, 4, 1, 300, 2, snr_db=30, seed=724, corrupt_fcs=True),
+               gp.gen_batch(g.F_VHT, 3, 1, 300, 2, snr_db=30, seed=722, l_len_short=3)]
+    return [gp.gen_batch(g.F_HT, 15, 2, 1100, n, snr_db=33, seed=800), gp.gen_batch(g.F_VHT, 7, 2, 700, n, snr_db=33, seed=801),
+            gp.gen_batch(g.F_HT, 11, 2, 250, n, snr_db=33, short_gi=True, seed=802),
+            gp.gen_batch(g.F_L, 5, 1, 200, n, snr_db=30, seed=803, nrx=2),
+            gp.gen_batch(g.F_VHT, 2, 1, 150, n, snr_db=30, seed=804, nrx=2)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nant", [1, 2])
+@pytest.mark.parametrize("chunks", [(0, 8192), (1000, 700), (4099, 8192)])
+def test_demod_block_stream_is_the_reference_stream(refgr, ours, nant, chunks):
+    pk = packets_of(mixed_batches(nant))
+    ref_out = refgr.run_demod(refgr.make_sig_stream(pk, nant=nant))
+    our_out = ours.run_demod(ours.make_sig_stream(pk, nant=nant), chunk_in=chunks[0], chunk_out=chunks[1])
+    same_llr_stream(our_out, ref_out)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunks", [(0, 8192), (777, 8192)])
+def test_decode_block_messages_are_the_reference_messages(refgr, ours, chunks):
+    """Reference demod -> our decode, our demod -> reference decode, and the all-ours chain."""
+    pk = packets_of(mixed_batches(1))
+    ref_llr = refgr.run_demod(refgr.make_sig_stream(pk))
+    ref_msgs = refgr.run_decode(ref_llr)
+    assert len(ref_msgs) >= 18
+    ref_pkts = refgr.split_llr_stream(ref_llr)
+    assert ours.run_decode(ours.make_llr_stream(ref_pkts), chunk_in=chunks[0]) == ref_msgs
+    our_llr = ours.run_demod(ours.make_sig_stream(pk), chunk_in=chunks[0])
+    assert ours.run_decode(our_llr, chunk_in=chunks[0]) == ref_msgs
+    assert refgr.run_decode(refgr.make_llr_stream(ours.split_llr_stream(our_llr))) == ref_msgs
+
+
+@pytest.mark.gpu
+def test_small_batches_from_the_environment(refgr, ours, monkeypatch):
+    """W80211_MAX_BATCH = 2: many GPU calls instead of one; the streams do not change."""
+    monkeypatch.setenv("W80211_MAX_BATCH", "2")
+    pk = packets_of(mixed_batches(1, n=2))
+    ref_llr = refgr.run_demod(refgr.make_sig_stream(pk))
+    our_llr = ours.run_demod(ours.make_sig_stream(pk))
+    same_llr_stream(our_llr, ref_llr)
+    assert ours.run_decode(our_llr) == refgr.run_decode(ref_llr)
+
+
+def _capture_stdout(fn):
+    import tempfile
+    sys.stdout.flush()
+    with tempfile.TemporaryFile() as tf:
+        old = os.dup(1)
+        os.dup2(tf.fileno(), 1)
+        try:
+            r = fn()
+        finally:
+            os.dup2(old, 1)
+            os.close(old)
+        tf.seek(0)
+        return r, tf.read().decode()
+
+
+@pytest.mark.gpu
+def test_decode_debug_lines(refgr, ours):
+    """ifdebug = true: the same 'crc32 correct / wrong' lines with the same counters (decode_impl.cc:376-509)."""
+    pk = packets_of(mixed_batches(1, n=2))
+    ref_llr = refgr.run_demod(refgr.make_sig_stream(pk))
+    ref_pkts = refgr.split_llr_stream(ref_llr)
+    m1, t1 = _capture_stdout(lambda: refgr.run_decode(refgr.make_llr_stream(ref_pkts), debug=True))
+    m2, t2 = _capture_stdout(lambda: ours.run_decode(ours.make_llr_stream(ref_pkts), debug=True))
+    assert m1 == m2
+    l1 = [x for x in t1.splitlines() if x.startswith("ieee80211 decode")]
+    l2 = [x for x in t2.splitlines() if x.startswith("ieee80211 decode")]
+    assert l1 and l1 == l2
+
+
+def test_blocks_without_a_gpu_drop_packets_and_say_so(refgr, capfd):
+    """No CUDA device: the blocks log the failure, consume their input and emit nothing -- no CPU path, no exception
+    out of general_work (reference blocks never throw either)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("needs a machine without a GPU")
+    if not os.path.exists(OURS_PATH):
+        pytest.skip("harness not built")
+    ours = refgr.load_harness(OURS_PATH)
+    pk = packets_of([gp.gen_batch(g.F_L, 3, 1, 100, 2, snr_db=30, seed=1)])
+    s = ours.make_sig_stream(pk)
+    out = ours.run_demod(s)
+    assert out.data().size == 0 and out.tags() == []
+    assert "no usable CUDA device" in capfd.readouterr().err
