@@ -221,7 +221,7 @@ def main_gpu(args):
              "mpdus": torch.empty(mp_cap_e * 16, dtype=torch.uint8).pin_memory()}
         bo = host.BatchOut()
         bo.mem = host.MEM_HOST
-        bo.desc, bo.bytes, bo.bytes_cap_eacity = t["desc"].data_ptr(), t["bytes"].data_ptr(), bytes_cap_e
+        bo.desc, bo.bytes, bo.bytes_capacity = t["desc"].data_ptr(), t["bytes"].data_ptr(), bytes_cap_e
         bo.psdu_off, bo.mpdus, bo.mpdu_capacity = t["psdu_off"].data_ptr(), t["mpdus"].data_ptr(), mp_cap_e
         return bo, t
 
@@ -239,7 +239,7 @@ def main_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    stage = {k: 0.0 for k in ("header", "demod", "viterbi", "traceback", "post", "total")}
+    stage = {k: 0.0 for k in ("header", "demod", "viterbi", "traceback", "post", "total", "host_plan", "host_collect")}
     counters = {"launches": 0}
 
     def run_steps(nsteps, bi, bos, tally, depth=2):
@@ -374,10 +374,11 @@ def main_gpu(args):
         from oracle import refgr
         if refgr.available():
             cores = host_cores()
-            gbps, ok, n, slowest, wall = run_reference_sample(cores, args.ref_packets)
+            npc = max(args.ref_packets, 1024)
+            gbps, ok, n, slowest, wall = run_reference_sample(cores, npc)
             line["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": cores, "kind": "reference",
                                     "sample": "%d packets of the same workload per core on %d cores, %.1f s; reference demod + decode blocks built unchanged (oracle/_ref), mock scheduler; %d/%d FCS ok"
-                                              % (args.ref_packets, cores, slowest, ok, n)}
+                                              % (npc, cores, slowest, ok, n)}
     print(json.dumps(line))
     rx.close()
     if dist is not None:
@@ -395,7 +396,7 @@ def main():
                     help="packets per step and GPU (0 = two full waves of the Viterbi kernel: SMs x 12 x 32 x 2)")
     ap.add_argument("--e2e-packets", type=int, default=0, help="packets per step and GPU of the host-fed leg (0 = SMs x 12 x 32 / 2)")
     ap.add_argument("--mpdu-len", type=int, default=4088, help="profiling only: shorter packets; the reported workload is the default")
-    ap.add_argument("--ref-packets", type=int, default=96, help="packets per core and step for the CPU reference")
+    ap.add_argument("--ref-packets", type=int, default=512, help="packets per core and step for the CPU reference")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     global MPDU_LEN

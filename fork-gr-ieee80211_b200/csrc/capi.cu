@@ -18,6 +18,7 @@
  * the GPU works on one batch while the host plans the other.
  */
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -60,6 +61,7 @@ struct Slot {
     w80211_batch_out* out = nullptr;
     std::vector<uint32_t> h_psdu_off;
     w80211_timing timing = {};
+    float host_plan_ms = 0.f;
 };
 
 } // namespace
@@ -186,10 +188,11 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
             dec.push_back(p);
             s.trellis_steps += (uint64_t)d.trellis;
         }
-        std::stable_sort(dec.begin(), dec.end(), [&](int a, int b) {
+        auto before = [&](int a, int b) {
             if (hd[a].cr != hd[b].cr) return hd[a].cr < hd[b].cr;
             return hd[a].trellis > hd[b].trellis;
-        });
+        };
+        if (!std::is_sorted(dec.begin(), dec.end(), before)) std::stable_sort(dec.begin(), dec.end(), before); /* homogeneous batches: nothing to do */
     }
     s.ndec = (int)dec.size();
     std::vector<int> slot_pkt, pkt_slot(npkt, -1);
@@ -388,7 +391,9 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
     if (npkt) CK(cudaMemcpyAsync(s.h_desc.p, s.desc.p, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     w80211_desc* hd = (w80211_desc*)s.h_desc.p;
+    const auto tp0 = std::chrono::steady_clock::now();
     RS(plan_and_upload(ctx, s, hd, true, do_decode));
+    s.host_plan_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tp0).count();
     CK(cudaEventRecord(s.ev[EV_PLAN], st));
     w_launch_demod(st, ctx->d_tab, s.nsymtot, npkt, in->nant, d_iq[0], d_iq[1], d_pk, (const w80211_desc*)s.desc.p,
                    (const int*)s.symprefix.p, (const float2*)s.chan.p, chan_stride, (float*)s.llr.p);
@@ -403,6 +408,7 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
     if (!s.busy) return fail(ctx, W80211_E_STATE, "slot idle: nothing to collect");
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(s.stream));
+    const auto tc0 = std::chrono::steady_clock::now();
     s.busy = false;
     w80211_batch_out* out = s.out;
     const w80211_desc* hd = (const w80211_desc*)s.h_desc.p;
@@ -426,9 +432,26 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
         uint32_t n = c[0];
         if (n > s.mpdu_cap) return fail(ctx, W80211_E_CAPACITY, "MPDU records overflow: %u > %u", n, s.mpdu_cap);
         w80211_mpdu* hm = (w80211_mpdu*)s.h_mpdus.p;
-        std::sort(hm, hm + n, [](const w80211_mpdu& a, const w80211_mpdu& b) {
-            return a.pkt != b.pkt ? a.pkt < b.pkt : a.off < b.off;
-        });
+        /* records arrive in completion order; put them in (pkt, off) order with one counting pass over the packets */
+        auto rec_before = [](const w80211_mpdu& a, const w80211_mpdu& b) { return a.pkt != b.pkt ? a.pkt < b.pkt : a.off < b.off; };
+        if (!std::is_sorted(hm, hm + n, rec_before)) {
+            std::vector<uint32_t> first((size_t)s.npkt + 1, 0);
+            bool in_range = true;
+            for (uint32_t i = 0; i < n; i++) {
+                if (hm[i].pkt >= (uint32_t)s.npkt) { in_range = false; break; }
+                first[hm[i].pkt + 1]++;
+            }
+            if (in_range) {
+                for (int p = 0; p < s.npkt; p++) first[(size_t)p + 1] += first[(size_t)p];
+                std::vector<w80211_mpdu> tmp(hm, hm + n);
+                std::vector<uint32_t> pos(first.begin(), first.end() - 1);
+                for (uint32_t i = 0; i < n; i++) hm[pos[tmp[i].pkt]++] = tmp[i];
+                for (int p = 0; p < s.npkt; p++)
+                    if (first[(size_t)p + 1] - first[(size_t)p] > 1) std::sort(hm + first[(size_t)p], hm + first[(size_t)p + 1], rec_before);
+            } else {
+                std::sort(hm, hm + n, rec_before);
+            }
+        }
         out->n_mpdu = n;
         out->n_crc_ok = c[1];
         out->psdu_bits_ok = (uint64_t)c[2] | ((uint64_t)c[3] << 32);
@@ -474,6 +497,8 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
     }
     t.total = ms(EV_START, EV_END);
     t.launches = s.launches;
+    t.host_plan = s.host_plan_ms;
+    t.host_collect = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tc0).count();
     cudaGetLastError();
     return 0;
 }

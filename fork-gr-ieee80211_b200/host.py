@@ -70,7 +70,7 @@ class Stats(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("h2d", C.c_float), ("header", C.c_float), ("demod", C.c_float), ("viterbi", C.c_float),
                 ("traceback", C.c_float), ("post", C.c_float), ("d2h", C.c_float), ("total", C.c_float),
-                ("launches", C.c_uint32)]
+                ("launches", C.c_uint32), ("host_plan", C.c_float), ("host_collect", C.c_float)]
 
 
 _lib = None

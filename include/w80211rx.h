@@ -155,6 +155,8 @@ typedef struct w80211_stats {
 typedef struct w80211_timing {
     float h2d, header, demod, viterbi, traceback, post, d2h, total;
     uint32_t launches; /* kernels launched for that batch */
+    float host_plan;    /* host wall time (ms) between the header kernel's results and the rest being enqueued */
+    float host_collect; /* host wall time (ms) spent in collect after the stream finished (record sort, counters) */
 } w80211_timing;
 
 int w80211_abi_version(void);

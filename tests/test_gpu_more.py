@@ -172,3 +172,26 @@ def test_full_size_batch_properties(rx):
     perm = np.random.default_rng(1).permutation(len(pk))
     res2 = rx.rx(iq, pk[perm], chan[perm])
     assert [m[3:-1] for m in res2.messages()] == [sent[i] for i in perm]
+
+
+def test_sharded_by_packet_equals_whole_batch(rx):
+    """a batch partitioned by packet (shard.partition, what each rank of a multi-GPU job gets) and
+    decoded shard by shard gives, merged in packet order, exactly the messages of the whole batch."""
+    shard = w80211rx.shard
+    bs = [gp.gen_batch(g.F_L, 6, 1, 700, 5, snr_db=30, seed=61), gp.gen_batch(g.F_HT, 5, 1, 1500, 5, snr_db=30, seed=62),
+          gp.gen_batch(g.F_VHT, 7, 1, 400, 5, snr_db=30, seed=63), gp.gen_batch(g.F_HT, 1, 1, 90, 5, snr_db=30, seed=64)]
+    iq, pkts, chan = host.pack_batch(bs)
+    whole = rx.rx(iq, pkts, chan)
+    per_pkt = {}
+    for m in whole.mpdus[: whole.n_mpdu]:
+        if m["crc_ok"]:
+            per_pkt.setdefault(int(m["pkt"]), []).append(whole.bytes[m["off"]: m["off"] + m["len"]].tobytes())
+    for world in (2, 3):
+        got = {}
+        for idx in shard.partition(pkts["nsamp"], world):
+            r = rx.rx(iq, pkts[idx], chan[idx])  # same sample arrays, a subset of the packet table
+            for m in r.mpdus[: r.n_mpdu]:
+                if m["crc_ok"]:
+                    got.setdefault(int(idx[m["pkt"]]), []).append(r.bytes[m["off"]: m["off"] + m["len"]].tobytes())
+        assert got == per_pkt
+    assert len(per_pkt) == 20

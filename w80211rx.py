@@ -12,3 +12,4 @@ pkg = importlib.import_module(PKG)
 gen = importlib.import_module(PKG + ".gen")
 gen_ppdu = importlib.import_module(PKG + ".gen_ppdu")
 host = importlib.import_module(PKG + ".host")
+shard = importlib.import_module(PKG + ".shard")
