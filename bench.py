@@ -196,6 +196,13 @@ def main_gpu(args):
     iq_host = iq_dev[:PE * nsamp].cpu().pin_memory()
     pk_host = torch.from_numpy(pk[:PE].view(np.uint8).copy()).pin_memory()
     ch_host = torch.from_numpy(chan[:PE].view(np.float32).reshape(-1).copy()).pin_memory()
+    # the same packets in the sc16 wire format: int16 pairs + one scale per packet
+    q_u, pk16_u, _ = host.quantize_sc16(iq_u, pk_u)
+    reps_e = (PE + N_UNIQUE - 1) // N_UNIQUE
+    iq16_host = torch.from_numpy(np.tile(q_u[0], (reps_e, 1))[:PE * nsamp].copy()).pin_memory()
+    pk16 = pk[:PE].copy()
+    pk16["iq_scale"] = np.tile(pk16_u["iq_scale"], reps_e)[:PE]
+    pk16_host = torch.from_numpy(pk16.view(np.uint8).copy()).pin_memory()
 
     rx = host.Receiver(local, nslots=2)
     bytes_cap = P * (MPDU_LEN + 72) + 4096
@@ -230,6 +237,9 @@ def main_gpu(args):
     bi_host = host.Receiver.make_in([iq_host.data_ptr()], pk_host.data_ptr(), ch_host.data_ptr(), mem=host.MEM_DEVICE,
                                     nsamples=PE * nsamp, npkt=PE)
     bi_host.mem = host.MEM_HOST
+    bi_host16 = host.Receiver.make_in([iq16_host.data_ptr()], pk16_host.data_ptr(), ch_host.data_ptr(), mem=host.MEM_DEVICE,
+                                      nsamples=PE * nsamp, npkt=PE, iq_format=host.IQ_SC16)
+    bi_host16.mem = host.MEM_HOST
     bo_d = [dev_out() for _ in range(2)]
     bo_h = [host_out() for _ in range(2)]
     L, h = rx.L, rx.h
@@ -290,28 +300,33 @@ def main_gpu(args):
     t_to = clocks.mark()
     launches = counters["launches"] * args.steps // KSEQ
 
-    # ---- end-to-end leg: pinned host buffers -> C ABI -> pinned host results, two slots in flight
-    run_steps(2, bi_host, bo_h, False)
-    barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    e2e_bits, _ = run_steps(args.steps, bi_host, bo_h, False)
-    barrier()
-    f1.record()
-    f1.synchronize()
-    e2e_ms = f0.elapsed_time(f1)
+    # ---- end-to-end legs: pinned host buffers -> C ABI -> pinned host results, two slots in flight
+    def e2e_leg(bi):
+        run_steps(2, bi, bo_h, False)
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        nbits, _ = run_steps(args.steps, bi, bo_h, False)
+        barrier()
+        f1.record()
+        f1.synchronize()
+        return nbits, f0.elapsed_time(f1)
+
+    e2e32_bits, e2e32_ms = e2e_leg(bi_host)    # fc32 samples on the wire (8 B per sample)
+    e2e_bits, e2e_ms = e2e_leg(bi_host16)      # sc16 samples on the wire (4 B per sample): the headline host-fed figure
     clk = clocks.stop(t_from, t_to)
-    h2d = PE * nsamp * 8 + pk_host.numel() + ch_host.numel() * 4
+    h2d = PE * nsamp * 4 + pk_host.numel() + ch_host.numel() * 4
+    h2d32 = PE * nsamp * 8 + pk_host.numel() + ch_host.numel() * 4
     d2h = int(bo_h[0][0].n_bytes) + int(bo_h[0][0].n_mpdu) * 16 + 64 + PE * host.DESC_DTYPE.itemsize
 
     # ---- max over ranks, totals over ranks
-    vals = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
-    sums = torch.tensor([float(bits), float(npk_ok), float(e2e_bits), float(launches)], dtype=torch.float64, device=dev)
+    vals = torch.tensor([ms, e2e_ms, e2e32_ms], dtype=torch.float64, device=dev)
+    sums = torch.tensor([float(bits), float(npk_ok), float(e2e_bits), float(launches), float(e2e32_bits)], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
         dist.all_reduce(sums, op=dist.ReduceOp.SUM)
-    ms, e2e_ms = vals.tolist()
-    bits, npk_ok, e2e_bits, launches = sums.tolist()
+    ms, e2e_ms, e2e32_ms = vals.tolist()
+    bits, npk_ok, e2e_bits, launches, e2e32_bits = sums.tolist()
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -351,7 +366,10 @@ def main_gpu(args):
         "packets_per_s": npk_ok / (ms * 1e-3), "fcs_ok_per_step": npk_ok / K / world,
         "e2e": {"value": e2e_bits / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / K, "packets_per_step_per_gpu": PE,
+                "iq_wire_format": "sc16 + one scale per packet (SURVEY.md 8(f) N2), expanded to fc32 on the GPU",
                 "note": "pinned host buffers through w80211_rx_submit/collect, 2 slots in flight; PCIe-bound, so smaller batches than the resident leg"},
+        "e2e_fc32": {"value": e2e32_bits / (e2e32_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d32, "d2h_bytes_per_step": d2h,
+                     "ms_per_step": e2e32_ms / K, "iq_wire_format": "fc32, the reference flowgraph's sample type"},
         "gpu_launches": int(launches),
         "clocks": clk,
         "stage_ms_per_step": {k: v / KSEQ for k, v in stage.items()},

@@ -47,7 +47,7 @@ struct Slot {
     cudaEvent_t ev[EV_COUNT] = {};
     bool busy = false;
     /* device */
-    DevBuf iq[2], pkts, chan_in, desc, chan, symprefix, llr, surv, bits, bytes, mpdus, counters, slot_pkt, pkt_slot, grp,
+    DevBuf iq[2], iq_raw[2], pkts, chan_in, desc, chan, symprefix, llr, surv, bits, bytes, mpdus, counters, slot_pkt, pkt_slot, grp,
         dec_list, psdu_off;
     /* pinned */
     PinBuf h_desc, h_plan, h_mpdus, h_counters;
@@ -340,8 +340,9 @@ int finish_outputs(w80211_ctx* ctx, Slot& s)
 int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_batch_out* out, bool do_decode)
 {
     if (!in || !out || in->npkt < 0 || (in->nant != 1 && in->nant != 2) || !in->iq[0] || (in->nant == 2 && !in->iq[1]) ||
-        (in->npkt > 0 && (!in->pkts || !in->chan)))
+        (in->npkt > 0 && (!in->pkts || !in->chan)) || (in->iq_format != W80211_IQ_FC32 && in->iq_format != W80211_IQ_SC16))
         return fail(ctx, W80211_E_ARG, "bad batch_in");
+    const bool sc16 = in->iq_format == W80211_IQ_SC16;
     if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy: collect it first");
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = s.stream;
@@ -361,11 +362,6 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
     const w80211_pkt_in* d_pk;
     const float2* d_chin;
     if (s.in_host) {
-        for (int a = 0; a < in->nant; a++) {
-            RS(dev_reserve(ctx, s.iq[a], (size_t)in->nsamples * 8 + 1024));
-            CK(cudaMemcpyAsync(s.iq[a].p, in->iq[a], (size_t)in->nsamples * 8, cudaMemcpyHostToDevice, st));
-            d_iq[a] = (const float2*)s.iq[a].p;
-        }
         RS(dev_reserve(ctx, s.pkts, (size_t)npkt * sizeof(w80211_pkt_in) + 16));
         RS(dev_reserve(ctx, s.chan_in, (size_t)npkt * 512 + 16));
         if (npkt) {
@@ -374,10 +370,38 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
         }
         d_pk = (const w80211_pkt_in*)s.pkts.p;
         d_chin = (const float2*)s.chan_in.p;
+        for (int a = 0; a < in->nant; a++) {
+            RS(dev_reserve(ctx, s.iq[a], (size_t)in->nsamples * 8 + 1024));
+            if (sc16) {
+                RS(dev_reserve(ctx, s.iq_raw[a], (size_t)in->nsamples * 4 + 1024));
+                CK(cudaMemcpyAsync(s.iq_raw[a].p, in->iq[a], (size_t)in->nsamples * 4, cudaMemcpyHostToDevice, st));
+            } else {
+                CK(cudaMemcpyAsync(s.iq[a].p, in->iq[a], (size_t)in->nsamples * 8, cudaMemcpyHostToDevice, st));
+            }
+            d_iq[a] = (const float2*)s.iq[a].p;
+        }
+        if (sc16) {
+            w_launch_sc16_to_fc32(st, npkt, in->nant, d_pk, s.iq_raw[0].p, s.iq_raw[1].p, (float2*)s.iq[0].p, (float2*)s.iq[1].p,
+                                  in->nsamples);
+            CK(cudaGetLastError());
+            if (npkt) s.launches += 1;
+        }
     } else {
-        for (int a = 0; a < in->nant; a++) d_iq[a] = (const float2*)in->iq[a];
         d_pk = in->pkts;
         d_chin = (const float2*)in->chan;
+        for (int a = 0; a < in->nant; a++) {
+            if (sc16) {
+                RS(dev_reserve(ctx, s.iq[a], (size_t)in->nsamples * 8 + 1024));
+                d_iq[a] = (const float2*)s.iq[a].p;
+            } else {
+                d_iq[a] = (const float2*)in->iq[a];
+            }
+        }
+        if (sc16) {
+            w_launch_sc16_to_fc32(st, npkt, in->nant, d_pk, in->iq[0], in->iq[1], (float2*)s.iq[0].p, (float2*)s.iq[1].p, in->nsamples);
+            CK(cudaGetLastError());
+            if (npkt) s.launches += 1;
+        }
     }
     CK(cudaEventRecord(s.ev[EV_H2D], st));
     RS(dev_reserve(ctx, s.desc, (size_t)npkt * sizeof(w80211_desc) + 16));
@@ -566,7 +590,7 @@ void w80211_destroy(w80211_ctx* ctx)
     for (int i = 0; i < 4; i++) {
         Slot& s = ctx->slots[i];
         if (s.stream) cudaStreamSynchronize(s.stream);
-        DevBuf* db[] = {&s.iq[0], &s.iq[1], &s.pkts, &s.chan_in, &s.desc, &s.chan, &s.symprefix, &s.llr, &s.surv, &s.bits,
+        DevBuf* db[] = {&s.iq[0], &s.iq[1], &s.iq_raw[0], &s.iq_raw[1], &s.pkts, &s.chan_in, &s.desc, &s.chan, &s.symprefix, &s.llr, &s.surv, &s.bits,
                         &s.bytes, &s.mpdus, &s.counters, &s.slot_pkt, &s.pkt_slot, &s.grp, &s.dec_list, &s.psdu_off};
         for (DevBuf* b : db)
             if (b->p) cudaFree(b->p);

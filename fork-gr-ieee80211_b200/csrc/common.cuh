@@ -70,6 +70,35 @@ __device__ __forceinline__ cf32 c_div(cf32 n, cf32 d)
     double y = __ddiv_rn(__dsub_rn(__dmul_rn(b, c), __dmul_rn(a, dd)), denom);
     return c_make(__double2float_rn(x), __double2float_rn(y));
 }
+/* The same quotients with the divisor known in advance (one channel tap serves every symbol of a packet):
+ * y = RN(1/b) once, then q0 = RN(a*y), e = a - b*q0 (exact in an FMA), q = RN(q0 + e*y).  With y the correctly
+ * rounded reciprocal this is RN(a/b) for every a (Markstein; Brisebarre, Muller, Raina, "Accelerating correctly
+ * rounded floating-point division when the divisor is known in advance", IEEE TC 2004) unless the significand of
+ * b is all ones, which the callers test for and send to the plain division.  tools/divcheck.cu compares both
+ * paths on random operands on the GPU. */
+__device__ __forceinline__ bool d_recip_unsafe(double b) { return (__double2hiint(b) & 0x000fffff) == 0x000fffff && __double2loint(b) == -1; }
+__device__ __forceinline__ bool f_recip_unsafe(float b) { return (__float_as_uint(b) & 0x007fffffu) == 0x007fffffu; }
+__device__ __forceinline__ double d_div_known(double a, double b, double y)
+{
+    double q0 = __dmul_rn(a, y);
+    double e = __fma_rn(-q0, b, a);
+    return __fma_rn(e, y, q0);
+}
+__device__ __forceinline__ float f_div_known(float a, float b, float y)
+{
+    float q0 = __fmul_rn(a, y);
+    float e = __fmaf_rn(-q0, b, a);
+    return __fmaf_rn(e, y, q0);
+}
+/* c_div with denom = c*c + d*d and y = RN(1/denom) precomputed (same rounding as c_div: the products of two
+ * binary32 values are exact in binary64, so fma(b, d, a*c) = RN(RN(a*c) + RN(b*d))) */
+__device__ __forceinline__ cf32 c_div_known(cf32 n, cf32 d, double denom, double y)
+{
+    double a = n.x, b = n.y, c = d.x, dd = d.y;
+    double nx = __fma_rn(b, dd, __dmul_rn(a, c));
+    double ny = __fma_rn(-a, dd, __dmul_rn(b, c));
+    return c_make(__double2float_rn(d_div_known(nx, denom, y)), __double2float_rn(d_div_known(ny, denom, y)));
+}
 /* std::abs(std::complex<float>) = hypotf */
 __device__ __forceinline__ float c_abs(cf32 a)
 {
@@ -141,6 +170,8 @@ void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nan
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nsymtot, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* sym_prefix,
                     const float2* chan, int chan_stride, float* llr);
+void w_launch_sc16_to_fc32(cudaStream_t st, int npkt, int nant, const w80211_pkt_in* pkts, const void* raw0, const void* raw1,
+                           float2* out0, float2* out1, unsigned long long nsamples);
 int w_launch_viterbi(cudaStream_t st, const int* cr_first, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
                      const float* llr, uint2* surv);
 void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,

@@ -74,6 +74,14 @@ __device__ __forceinline__ void qam_llr(cf32 q, int nb, const uint16_t* __restri
     axis_llr(q.y, half, map, j * nb + half, out);
 }
 
+/* a / f with y = RN(1/f); tiny quotients (where the FMA residual could underflow) and unsafe divisors take the plain division */
+__device__ __forceinline__ cf32 c_divf_known(cf32 a, float f, float y, bool slow)
+{
+    float qx = f_div_known(a.x, f, y), qy = f_div_known(a.y, f, y);
+    if (slow || (fabsf(qx) < 1e-30f && a.x != 0.0f) || (fabsf(qy) < 1e-30f && a.y != 0.0f)) return c_divf(a, f);
+    return c_make(qx, qy);
+}
+
 __device__ __forceinline__ float shfl_f(float v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
 __device__ __forceinline__ void load_sym(const float2* __restrict__ src, int g, bool valid, float2* v)
@@ -112,6 +120,15 @@ __device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, 
     c8_fft8(re, im);
 }
 
+/* dynamic shared memory of one block (the two-antenna variant needs more than the 48 KB static limit) */
+template <bool MIMO>
+struct DemodSmem {
+    double2 eqc[DEMOD_GROUPS][64];                                 /* per bin: |H|^2 in binary64 and its reciprocal */
+    float stage[DEMOD_GROUPS][MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2]; /* one symbol's LLRs per group, deinterleaved */
+    float2 xch[DEMOD_GROUPS][W_FFT_XCH_FLOAT2];                    /* FFT exchange */
+    uint16_t smap[DEMOD_GROUPS][MIMO ? 2 * W_MAPLEN : W_MAPLEN];   /* the item's deinterleave table(s) */
+};
+
 template <bool MIMO> /* MIMO = false: one antenna, no two-stream code or registers at all */
 __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_kernel(const W80211Tables* __restrict__ T, int nitems, int npkt, int nant,
                                                               const float2* __restrict__ iq0, const float2* __restrict__ iq1,
@@ -119,8 +136,12 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
                                                               const w80211_desc* __restrict__ desc, const int* __restrict__ item_prefix,
                                                               const float2* __restrict__ chan, int chan_stride, float* __restrict__ llr)
 {
-    __shared__ float2 xch[DEMOD_GROUPS][W_FFT_XCH_FLOAT2];
-    __shared__ __align__(16) float stage[DEMOD_GROUPS][MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2];
+    extern __shared__ __align__(16) unsigned char demod_smem_raw[];
+    DemodSmem<MIMO>& S = *reinterpret_cast<DemodSmem<MIMO>*>(demod_smem_raw);
+    auto& xch = S.xch;
+    auto& stage = S.stage;
+    auto& eqc = S.eqc;
+    auto& smap = S.smap;
     const int tid = threadIdx.x;
     const int lane = tid & 31, g = tid & 7, base = lane & ~7, grp = tid >> 3;
     const int w = blockIdx.x * DEMOD_GROUPS + grp;
@@ -159,6 +180,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     const int8_t* binj = fmt == W80211_F_L ? T->bin_j_l : T->bin_j_nl;
     int jj[8];
     cf32 hh[8];
+    bool slow_div = false; /* a divisor with an all-ones significand: take the plain division (never seen in practice) */
 #pragma unroll
     for (int k2 = 0; k2 < 8; k2++) {
         int i = g + 8 * k2;
@@ -170,13 +192,28 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             float2 h = __ldg(&H[i]);
             hh[k2] = c_make(h.x, h.y);
         }
+        /* the divisor of Y/H is the same for every symbol of the packet: |H|^2 and RN(1/|H|^2) once per item */
+        const double hc = hh[k2].x, hd = hh[k2].y;
+        const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
+        slow_div = slow_div || d_recip_unsafe(denom);
+        eqc[grp][i] = make_double2(denom, __drcp_rn(denom));
     }
     const int z = fmt == W80211_F_L ? 1 : (fmt == W80211_F_HT ? 3 : 4);
     const bool ht2 = two && fmt == W80211_F_HT;
     const int nbi = nb == 1 ? 0 : (nb == 2 ? 1 : (nb == 4 ? 2 : (nb == 6 ? 3 : 4)));
     const int tid1 = fmt == W80211_F_L ? nbi : (two ? 9 + nbi : 4 + nbi);
-    const uint16_t* map1 = T->map[tid1];
-    const uint16_t* map2 = T->map[14 + nbi];
+    {
+        const int nmap = (fmt == W80211_F_L ? 48 : 52) * nb;
+        const uint16_t* gm1 = T->map[tid1];
+        const uint16_t* gm2 = T->map[14 + nbi];
+        for (int k = g; k < nmap; k += 8) {
+            smap[grp][k] = gm1[k];
+            if (MIMO) smap[grp][W_MAPLEN + k] = gm2[k];
+        }
+        __syncwarp();
+    }
+    const uint16_t* map1 = smap[grp];
+    const uint16_t* map2 = smap[grp] + (MIMO ? W_MAPLEN : 0);
     cf32 R[2][4];
 #pragma unroll
     for (int s2 = 0; s2 < 2; s2++)
@@ -212,7 +249,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             e2[k2] = c_make(0.f, 0.f);
             if (act && jj[k2] >= -1) {
                 if (!two) {
-                    e1[k2] = c_div(c_make(re[k2], im[k2]), hh[k2]);
+                    const double2 q = eqc[grp][i];
+                    e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], q.x, q.y);
                 } else {
                     const float4* H4 = reinterpret_cast<const float4*>(H + i * 4);
                     const float4* I4 = reinterpret_cast<const float4*>(H + 256 + i * 4);
@@ -268,15 +306,18 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             }
             const cf32 ps = c_conj(sum);
             const float pa = c_abs(ps);
+            /* q = eq * conj(sum) / |sum|: one divisor per symbol */
+            const bool slow_pa = f_recip_unsafe(pa) || !(pa > 1e-30f) || !(pa < 1e30f);
+            const float rpa = __frcp_rn(pa);
             /* LLRs through the combined deinterleave / de-parse table into the shared staging block */
 #pragma unroll
             for (int k2 = 0; k2 < 8; k2++) {
                 int j = jj[k2];
                 if (j >= 0) {
-                    cf32 q = c_divf(c_mul(e1[k2], ps), pa);
+                    cf32 q = c_divf_known(c_mul(e1[k2], ps), pa, rpa, slow_pa);
                     qam_llr(q, nb, map1, j, stg);
                     if (two) {
-                        cf32 q2 = c_divf(c_mul(e2[k2], ps), pa);
+                        cf32 q2 = c_divf_known(c_mul(e2[k2], ps), pa, rpa, slow_pa);
                         qam_llr(q2, nb, map2, j, stg);
                     }
                 }
@@ -304,8 +345,14 @@ void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nitems, int np
 {
     if (nitems <= 0) return;
     int blocks = (nitems + DEMOD_GROUPS - 1) / DEMOD_GROUPS;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(demod_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<true>));
+        cudaFuncSetAttribute(demod_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<false>));
+        attr_set = true;
+    }
     if (nant == 2)
-        demod_kernel<true><<<blocks, DEMOD_THREADS, 0, st>>>(tab, nitems, npkt, nant, iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
+        demod_kernel<true><<<blocks, DEMOD_THREADS, sizeof(DemodSmem<true>), st>>>(tab, nitems, npkt, nant, iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
     else
-        demod_kernel<false><<<blocks, DEMOD_THREADS, 0, st>>>(tab, nitems, npkt, nant, iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
+        demod_kernel<false><<<blocks, DEMOD_THREADS, sizeof(DemodSmem<false>), st>>>(tab, nitems, npkt, nant, iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
 }

@@ -29,15 +29,16 @@ class Cfg(C.Structure):
 
 class PktIn(C.Structure):
     _fields_ = [("iq_offset", C.c_uint64), ("nsamp", C.c_int32), ("l_mcs", C.c_int32), ("l_len", C.c_int32),
-                ("cfo", C.c_float), ("snr", C.c_float), ("rssi", C.c_float)]
+                ("cfo", C.c_float), ("snr", C.c_float), ("rssi", C.c_float), ("iq_scale", C.c_float)]
 
 
 PKT_IN_DTYPE = np.dtype([("iq_offset", "<u8"), ("nsamp", "<i4"), ("l_mcs", "<i4"), ("l_len", "<i4"),
-                         ("cfo", "<f4"), ("snr", "<f4"), ("rssi", "<f4")], align=True)
+                         ("cfo", "<f4"), ("snr", "<f4"), ("rssi", "<f4"), ("iq_scale", "<f4")], align=True)
+IQ_FC32, IQ_SC16 = 0, 1
 
 
 class BatchIn(C.Structure):
-    _fields_ = [("npkt", C.c_int32), ("nant", C.c_int32), ("mem", C.c_int32), ("reserved", C.c_int32),
+    _fields_ = [("npkt", C.c_int32), ("nant", C.c_int32), ("mem", C.c_int32), ("iq_format", C.c_int32),
                 ("iq", C.c_void_p * 2), ("nsamples", C.c_uint64), ("pkts", C.c_void_p), ("chan", C.c_void_p)]
 
 
@@ -132,6 +133,25 @@ def pack_batch(batches):
     return [np.concatenate(x) for x in iq], np.concatenate(pk), np.concatenate(ch)
 
 
+def quantize_sc16(iq, pkts, headroom=0.9):
+    """fc32 packets -> the sc16 wire format: per packet, scale = max |component| / (32767 * headroom),
+    sample = round(x / scale).  Returns (int16 arrays [nsamples, 2], packet table with iq_scale set, the complex64
+    arrays a receiver of those int16 values reconstructs: (float)int16 * scale -- the reference's input for parity)."""
+    pk = pkts.copy()
+    q = [np.zeros((len(x), 2), np.int16) for x in iq]
+    back = [np.zeros(len(x), np.complex64) for x in iq]
+    for p in range(len(pk)):
+        o, n = int(pk["iq_offset"][p]), int(pk["nsamp"][p])
+        peak = max(float(np.abs(x[o:o + n].view(np.float32)).max()) if n else 0.0 for x in iq)
+        scale = np.float32(peak / (32767.0 * headroom)) if peak > 0 else np.float32(1.0)
+        pk["iq_scale"][p] = scale
+        for a, x in enumerate(iq):
+            v = np.rint(x[o:o + n].view(np.float32).astype(np.float64) / float(scale)).astype(np.int16).reshape(-1, 2)
+            q[a][o:o + n] = v
+            back[a][o:o + n] = (v.astype(np.float32) * scale).reshape(-1).view(np.complex64)
+    return q, pk, back
+
+
 class Result:
     """Host-side view of one finished batch."""
 
@@ -187,16 +207,19 @@ class Receiver:
 
     # -- raw struct helpers -------------------------------------------------
     @staticmethod
-    def make_in(iq, pkts, chan, mem=MEM_HOST, nsamples=None, npkt=None):
-        """iq: list of numpy complex64 arrays (host) or integer device pointers (device)."""
+    def make_in(iq, pkts, chan, mem=MEM_HOST, nsamples=None, npkt=None, iq_format=None):
+        """iq: list of numpy arrays (host: complex64, or int16 of shape [nsamples, 2] for sc16) or integer device pointers."""
         bi = BatchIn()
         bi.nant = len(iq)
         bi.mem = mem
         if mem == MEM_HOST:
             bi.npkt = len(pkts)
             bi.nsamples = len(iq[0])
+            if iq_format is None:
+                iq_format = IQ_SC16 if iq[0].dtype == np.int16 else IQ_FC32
             for a, x in enumerate(iq):
-                assert x.dtype == np.complex64 and x.flags.c_contiguous
+                assert x.flags.c_contiguous
+                assert (x.dtype == np.complex64) if iq_format == IQ_FC32 else (x.dtype == np.int16 and x.ndim == 2 and x.shape[1] == 2)
                 bi.iq[a] = x.ctypes.data
             assert pkts.dtype == PKT_IN_DTYPE
             bi.pkts = pkts.ctypes.data
@@ -209,6 +232,7 @@ class Receiver:
                 bi.iq[a] = int(x)
             bi.pkts = int(pkts)
             bi.chan = int(chan)
+        bi.iq_format = int(iq_format or 0)
         return bi
 
     @staticmethod

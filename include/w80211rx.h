@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define W80211_ABI_VERSION 1
+#define W80211_ABI_VERSION 2
 
 /* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
 #define W80211_F_L 0
@@ -47,6 +47,11 @@ extern "C" {
 /* where the caller's sample / LLR / output buffers live */
 #define W80211_MEM_HOST 0   /* host memory (pinned or pageable); copies are part of the call */
 #define W80211_MEM_DEVICE 1 /* device memory of the ctx's GPU; nothing is copied */
+
+/* sample format of w80211_batch_in.iq[] (the IQ wire format of the host feed) */
+#define W80211_IQ_FC32 0 /* interleaved (re, im) binary32, what UHD hands to the reference's flowgraph */
+#define W80211_IQ_SC16 1 /* interleaved (re, im) int16, the native USRP wire format; sample = (float)int16 * pkt.iq_scale,
+                            one binary32 multiply per component, so a reference fed the same products sees identical input */
 
 /* error codes */
 #define W80211_OK 0
@@ -82,14 +87,15 @@ typedef struct w80211_pkt_in {
     int32_t l_mcs;      /* tag "mcs": legacy rate index 0..7 */
     int32_t l_len;      /* tag "len": L-SIG LENGTH */
     float cfo, snr, rssi; /* tags carried through to the output untouched */
+    float iq_scale;     /* W80211_IQ_SC16 only: value of one int16 unit for this packet */
 } w80211_pkt_in;
 
 typedef struct w80211_batch_in {
     int32_t npkt;
     int32_t nant;            /* 1: demod (lib/demod_impl.cc), 2: demod2 (lib/demod2_impl.cc) */
     int32_t mem;             /* W80211_MEM_HOST / W80211_MEM_DEVICE: applies to iq[], chan, pkts */
-    int32_t reserved;
-    const float* iq[2];      /* per antenna: interleaved (re,im) fc32 samples */
+    int32_t iq_format;       /* W80211_IQ_FC32 (0) or W80211_IQ_SC16 */
+    const void* iq[2];       /* per antenna: interleaved (re,im) samples, float or int16 according to iq_format */
     uint64_t nsamples;       /* length of each iq[] array in complex samples */
     const w80211_pkt_in* pkts; /* [npkt] */
     const float* chan;       /* [npkt][64][2]: tag "chan", legacy channel in natural FFT order (signal_impl.cc:143) */

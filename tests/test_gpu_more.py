@@ -195,3 +195,34 @@ def test_sharded_by_packet_equals_whole_batch(rx):
                     got.setdefault(int(idx[m["pkt"]]), []).append(r.bytes[m["off"]: m["off"] + m["len"]].tobytes())
         assert got == per_pkt
     assert len(per_pkt) == 20
+
+
+@pytest.mark.parametrize("nant", [1, 2])
+def test_sc16_wire_format(refgr, rx, nant):
+    """IQ as int16 pairs + one scale per packet.  The reference is fed the floats a host would
+    reconstruct ((float)int16 * scale); the GPU gets the int16 values: same tags, bit-identical LLRs, same messages."""
+    if nant == 1:
+        bs = [gp.gen_batch(g.F_VHT, 8, 1, 1500, 3, snr_db=30, seed=71), gp.gen_batch(g.F_L, 7, 1, 600, 3, snr_db=30, seed=72),
+              gp.gen_batch(g.F_HT, 7, 1, 800, 3, snr_db=30, short_gi=True, seed=73)]
+    else:
+        bs = [gp.gen_batch(g.F_HT, 15, 2, 900, 3, snr_db=33, seed=74), gp.gen_batch(g.F_VHT, 7, 2, 500, 3, snr_db=33, seed=75)]
+    iq, pkts, chan = host.pack_batch(bs)
+    q, pk16, back = host.quantize_sc16(iq, pkts)
+    assert q[0].dtype == np.int16 and np.abs(q[0]).max() <= 32767
+    res = rx.rx(q, pk16, chan, want_llr=True)
+    # the same packets as fc32 (the dequantised floats) through the reference blocks
+    packets = []
+    for p in range(len(pkts)):
+        o, n = int(pkts["iq_offset"][p]), int(pkts["nsamp"][p])
+        packets.append({"iq": [b[o:o + n] for b in back], "l_mcs": int(pkts["l_mcs"][p]), "l_len": int(pkts["l_len"][p]),
+                        "chan": chan[p], "seq": p})
+    ref_llr = refgr.run_demod(refgr.make_sig_stream(packets, nant=nant))
+    ref_pkts = refgr.split_llr_stream(ref_llr)
+    assert len(ref_pkts) == len(pkts)
+    for p, r in enumerate(ref_pkts):
+        assert np.array_equal(res.packet_llr(p), r["llr"]), "packet %d: LLRs differ" % p
+    assert res.messages() == refgr.run_decode(ref_llr)
+    assert len(res.messages()) == len(pkts)
+    # and through fc32 input of the same floats: identical to the sc16 path
+    res32 = rx.rx(back, pkts, chan, want_llr=True)
+    assert np.array_equal(res32.llr[: res32.n_llr], res.llr[: res.n_llr])
