@@ -40,46 +40,67 @@ __device__ __forceinline__ int find_packet(const int* __restrict__ prefix, int n
     return lo;
 }
 
-/* max-log LLRs of one axis value (already scaled), written through the deinterleave table */
-__device__ __forceinline__ void axis_llr(float v, int half, const uint16_t* __restrict__ map, int idx, float* __restrict__ out)
+/* max-log LLRs of one axis value (already scaled), written through the deinterleave table (procSymQamToLlr,
+ * cloud80211phy.cc:2090-2148); HALF = bits per axis, a compile-time constant so the chain has no branches */
+template <int HALF>
+__device__ __forceinline__ void axis_llr(float v, const uint16_t* __restrict__ map, float* __restrict__ out)
 {
-    out[map[idx]] = v;
-    if (half >= 2) {
-        float thr = half == 2 ? 2.0f : (half == 3 ? 4.0f : 8.0f);
+    out[map[0]] = v;
+    if (HALF >= 2) {
+        float thr = HALF == 2 ? 2.0f : (HALF == 3 ? 4.0f : 8.0f);
         float l = __fsub_rn(thr, fabsf(v));
-        out[map[idx + 1]] = l;
-        if (half >= 3) {
+        out[map[1]] = l;
+        if (HALF >= 3) {
             thr = __fmul_rn(thr, 0.5f);
             l = __fsub_rn(thr, fabsf(l));
-            out[map[idx + 2]] = l;
-            if (half >= 4) {
+            out[map[2]] = l;
+            if (HALF >= 4) {
                 l = __fsub_rn(2.0f, fabsf(l));
-                out[map[idx + 3]] = l;
+                out[map[3]] = l;
             }
         }
     }
 }
 
-__device__ __forceinline__ void qam_llr(cf32 q, int nb, const uint16_t* __restrict__ map, int j, float* __restrict__ out)
+template <int NB>
+__device__ __forceinline__ void qam_llr(cf32 q, const uint16_t* __restrict__ map /* + j * NB */, float* __restrict__ out)
 {
-    if (nb == 1) {
-        out[map[j]] = q.x;
+    if (NB == 1) {
+        out[map[0]] = q.x;
         return;
     }
     /* reference constants, cloud80211phy.cc:2105,2114,2125,2138 */
-    float sc = nb == 2 ? 1.4142135623730951f : (nb == 4 ? 3.1622776601683795f : (nb == 6 ? 6.48074069840786f : 13.038404810405298f));
+    const float sc = NB == 2 ? 1.4142135623730951f : (NB == 4 ? 3.1622776601683795f : (NB == 6 ? 6.48074069840786f : 13.038404810405298f));
     q = c_scale(q, sc);
-    int half = nb >> 1;
-    axis_llr(q.x, half, map, j * nb, out);
-    axis_llr(q.y, half, map, j * nb + half, out);
+    axis_llr<(NB >> 1)>(q.x, map, out);
+    axis_llr<(NB >> 1)>(q.y, map + (NB >> 1), out);
 }
 
-/* a / f with y = RN(1/f); tiny quotients (where the FMA residual could underflow) and unsafe divisors take the plain division */
+/* a / f with y = RN(1/f); unsafe divisors and tiny quotients (where the FMA residual could leave the normal range) take
+ * the plain division */
 __device__ __forceinline__ cf32 c_divf_known(cf32 a, float f, float y, bool slow)
 {
-    float qx = f_div_known(a.x, f, y), qy = f_div_known(a.y, f, y);
-    if (slow || (fabsf(qx) < 1e-30f && a.x != 0.0f) || (fabsf(qy) < 1e-30f && a.y != 0.0f)) return c_divf(a, f);
+    const float qx = f_div_known(a.x, f, y), qy = f_div_known(a.y, f, y);
+    if (slow || !(fabsf(qx) >= 1e-30f && fabsf(qy) >= 1e-30f)) return c_divf(a, f);
     return c_make(qx, qy);
+}
+
+/* the LLRs of one symbol: q = eq * conj(pilot sum) / |pilot sum| per data subcarrier, demapped and scattered into the
+ * group's staging block in coded-bit order */
+template <int NB, bool MIMO>
+__device__ __forceinline__ void symbol_llrs(const cf32 (&e1)[8], const cf32 (&e2)[8], const int (&jj)[8], bool two, cf32 ps, float pa,
+                                            const uint16_t* __restrict__ map1, const uint16_t* __restrict__ map2, float* __restrict__ stg)
+{
+    const bool slow_pa = f_recip_unsafe(pa) || !(pa > 1e-30f) || !(pa < 1e30f);
+    const float rpa = __frcp_rn(pa);
+#pragma unroll
+    for (int k2 = 0; k2 < 8; k2++) {
+        const int j = jj[k2];
+        if (j >= 0) {
+            qam_llr<NB>(c_divf_known(c_mul(e1[k2], ps), pa, rpa, slow_pa), map1 + j * NB, stg);
+            if (MIMO && two) qam_llr<NB>(c_divf_known(c_mul(e2[k2], ps), pa, rpa, slow_pa), map2 + j * NB, stg);
+        }
+    }
 }
 
 __device__ __forceinline__ float shfl_f(float v, int src) { return __shfl_sync(0xffffffffu, v, src); }
@@ -123,9 +144,9 @@ __device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, 
 /* dynamic shared memory of one block (the two-antenna variant needs more than the 48 KB static limit) */
 template <bool MIMO>
 struct DemodSmem {
-    double2 eqc[DEMOD_GROUPS][64];                                 /* per bin: |H|^2 in binary64 and its reciprocal */
-    float stage[DEMOD_GROUPS][MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2]; /* one symbol's LLRs per group, deinterleaved */
-    float2 xch[DEMOD_GROUPS][W_FFT_XCH_FLOAT2];                    /* FFT exchange */
+    double eqr[DEMOD_GROUPS][64];                                  /* per bin: RN(1 / |H|^2) in binary64 */
+    float stage[DEMOD_GROUPS][MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2]; /* one symbol's LLRs per group, deinterleaved; its first
+                                                                      576 bytes double as the FFT exchange area */
     uint16_t smap[DEMOD_GROUPS][MIMO ? 2 * W_MAPLEN : W_MAPLEN];   /* the item's deinterleave table(s) */
 };
 
@@ -138,9 +159,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
 {
     extern __shared__ __align__(16) unsigned char demod_smem_raw[];
     DemodSmem<MIMO>& S = *reinterpret_cast<DemodSmem<MIMO>*>(demod_smem_raw);
-    auto& xch = S.xch;
     auto& stage = S.stage;
-    auto& eqc = S.eqc;
+    auto& eqr = S.eqr;
     auto& smap = S.smap;
     const int tid = threadIdx.x;
     const int lane = tid & 31, g = tid & 7, base = lane & ~7, grp = tid >> 3;
@@ -172,8 +192,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     const bool two = MIMO && valid && nss == 2;
     const bool any2 = MIMO && __any_sync(0xffffffffu, two);
     const int nloop = __reduce_max_sync(0xffffffffu, nsy);
-    float2* myx = xch[grp];
     float* stg = stage[grp];
+    float2* myx = reinterpret_cast<float2*>(stg); /* used only inside the FFT, before the symbol's LLRs are staged */
 
     /* per-item constants: channel of the lane's eight bins (one stream), tables, pilot patterns */
     const float2* H = chan + (size_t)p * chan_stride;
@@ -196,7 +216,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
         const double hc = hh[k2].x, hd = hh[k2].y;
         const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
         slow_div = slow_div || d_recip_unsafe(denom);
-        eqc[grp][i] = make_double2(denom, __drcp_rn(denom));
+        eqr[grp][i] = __drcp_rn(denom);
     }
     const int z = fmt == W80211_F_L ? 1 : (fmt == W80211_F_HT ? 3 : 4);
     const bool ht2 = two && fmt == W80211_F_HT;
@@ -247,11 +267,13 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             int i = g + 8 * k2;
             e1[k2] = c_make(0.f, 0.f);
             e2[k2] = c_make(0.f, 0.f);
-            if (act && jj[k2] >= -1) {
-                if (!two) {
-                    const double2 q = eqc[grp][i];
-                    e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], q.x, q.y);
-                } else {
+            if (!MIMO || !two) {
+                /* every bin, used or not (unused bins divide by 1): no branch in the one-stream path */
+                const double hc = hh[k2].x, hd = hh[k2].y;
+                const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
+                e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, eqr[grp][i]);
+            } else if (act && jj[k2] >= -1) {
+                {
                     const float4* H4 = reinterpret_cast<const float4*>(H + i * 4);
                     const float4* I4 = reinterpret_cast<const float4*>(H + 256 + i * 4);
                     float4 ha = __ldg(H4), hb = __ldg(H4 + 1), ia = __ldg(I4), ib = __ldg(I4 + 1);
@@ -306,21 +328,14 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             }
             const cf32 ps = c_conj(sum);
             const float pa = c_abs(ps);
-            /* q = eq * conj(sum) / |sum|: one divisor per symbol */
-            const bool slow_pa = f_recip_unsafe(pa) || !(pa > 1e-30f) || !(pa < 1e30f);
-            const float rpa = __frcp_rn(pa);
-            /* LLRs through the combined deinterleave / de-parse table into the shared staging block */
-#pragma unroll
-            for (int k2 = 0; k2 < 8; k2++) {
-                int j = jj[k2];
-                if (j >= 0) {
-                    cf32 q = c_divf_known(c_mul(e1[k2], ps), pa, rpa, slow_pa);
-                    qam_llr(q, nb, map1, j, stg);
-                    if (two) {
-                        cf32 q2 = c_divf_known(c_mul(e2[k2], ps), pa, rpa, slow_pa);
-                        qam_llr(q2, nb, map2, j, stg);
-                    }
-                }
+            /* LLRs through the combined deinterleave / de-parse table into the shared staging block; one instance
+             * per modulation so the demapping chain is straight-line code */
+            switch (nb) {
+            case 1: symbol_llrs<1, MIMO>(e1, e2, jj, two, ps, pa, map1, map2, stg); break;
+            case 2: symbol_llrs<2, MIMO>(e1, e2, jj, two, ps, pa, map1, map2, stg); break;
+            case 4: symbol_llrs<4, MIMO>(e1, e2, jj, two, ps, pa, map1, map2, stg); break;
+            case 6: symbol_llrs<6, MIMO>(e1, e2, jj, two, ps, pa, map1, map2, stg); break;
+            default: symbol_llrs<8, MIMO>(e1, e2, jj, two, ps, pa, map1, map2, stg); break;
             }
         }
         __syncwarp();
