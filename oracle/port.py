@@ -1,0 +1,67 @@
+"""ctypes front end of oracle/libport80211.so (oracle/port/decode_port.c): the plain-C restatement of the reference's
+decode block.  TEST INFRASTRUCTURE ONLY -- see the header of decode_port.c."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libport80211.so")
+_lib = None
+
+
+def available():
+    return os.path.exists(_LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(_LIB_PATH)
+        vp, ci = C.c_void_p, C.c_int
+        L.port_viterbi.argtypes = [vp, ci, ci, ci, vp]
+        L.port_descramble.argtypes = [vp, vp, ci]
+        L.port_trellis_tables.argtypes = [vp, vp]
+        L.port_decode_packet.argtypes = [vp, ci, ci, ci, ci, ci, ci, ci, vp, ci, vp, vp]
+        _lib = L
+    return _lib
+
+
+def trellis_tables():
+    nx, lb = np.zeros(128, np.int32), np.zeros(128, np.int32)
+    lib().port_trellis_tables(nx.ctypes.data, lb.ctypes.data)
+    return nx.reshape(64, 2), lb.reshape(64, 2)
+
+
+def viterbi(llr, trellis, cr):
+    x = np.ascontiguousarray(llr, np.float32)
+    bits = np.zeros(trellis, np.uint8)
+    r = lib().port_viterbi(x.ctypes.data, x.size, trellis, cr, bits.ctypes.data)
+    if r < 0:
+        raise ValueError("port_viterbi: not enough LLRs or bad parameters")
+    return bits, r
+
+
+def decode_packet(p):
+    """p: dict with 'llr', 'format', 'mcs', 'len', 'cr', 'ampdu', 'trellis' (the decode block's tags) -> (messages, fcs failures)."""
+    x = np.ascontiguousarray(p["llr"], np.float32)
+    buf = np.zeros(3 * 4200 + 64, np.uint8)
+    nb, nf = C.c_int(0), C.c_int(0)
+    n = lib().port_decode_packet(x.ctypes.data, x.size, int(p["format"]), int(p["mcs"]), int(p["len"]), int(p["cr"]),
+                                 int(p["ampdu"]), int(p["trellis"]), buf.ctypes.data, buf.size, C.byref(nb), C.byref(nf))
+    if n < 0:
+        raise ValueError("port_decode_packet failed")
+    out, o = [], 0
+    for _ in range(n):
+        ln = int(buf[o]) | (int(buf[o + 1]) << 8)
+        out.append(buf[o + 2:o + 2 + ln].tobytes())
+        o += 2 + ln
+    return out, nf.value
+
+
+def run_decode(packets):
+    """List of packet dicts (oracle.refgr.split_llr_stream format) -> list of published blobs, in order."""
+    msgs = []
+    for p in packets:
+        msgs += decode_packet(p)[0]
+    return msgs
