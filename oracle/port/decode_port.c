@@ -48,6 +48,15 @@ int port_viterbi(const float* llr, int total, int trellis, int cr, uint8_t* bits
     if (cr < 0 || cr > 3 || trellis <= 0 || trellis > T_MAX) return -1;
     uint8_t* his = (uint8_t*)calloc((size_t)(trellis + 1) * 64, 1); /* his[t][state] = winning source */
     if (!his) return -1;
+    static int NEXT[64][2], LABEL[64][2], ready = 0;
+    if (!ready) {
+        for (int s = 0; s < 64; s++)
+            for (int b = 0; b < 2; b++) {
+                NEXT[s][b] = trellis_next(s, b);
+                LABEL[s][b] = trellis_label(s, b);
+            }
+        ready = 1;
+    }
     float a0[64], a1[64], *pre = a0, *cur = a1;
     for (int i = 0; i < 64; i++) a0[i] = a1[i] = -1000000000000000.0f;
     a0[0] = 0.0f;
@@ -64,8 +73,8 @@ int port_viterbi(const float* llr, int total, int trellis, int cr, uint8_t* bits
         uint8_t* h = his + (size_t)(t + 1) * 64;
         for (int s = 0; s < 64; s++)
             for (int b = 0; b < 2; b++) {
-                float cand = pre[s] + tab[trellis_label(s, b)];
-                int n = trellis_next(s, b);
+                float cand = pre[s] + tab[LABEL[s][b]];
+                int n = NEXT[s][b];
                 if (cand > cur[n]) {
                     cur[n] = cand;
                     h[n] = (uint8_t)s;
