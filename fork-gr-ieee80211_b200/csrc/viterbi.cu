@@ -298,11 +298,12 @@ __global__ void __launch_bounds__(32, VIT_MINBLK) viterbi_kernel(const int4* __r
 }
 
 /* vstb_end (decode_impl.cc:282-302): traceback from state 0 at the end of the trellis.  One thread
- * per packet; survivor words are read 32 steps (16 uint4, coalesced across the warp) at a time and
- * the decoded bits leave as one 32-bit word per 32 steps, bit i = decoded bit 32j+i. */
-__global__ void __launch_bounds__(32) traceback_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
-                                                       const w80211_desc* __restrict__ desc, const uint2* __restrict__ surv,
-                                                       uint32_t* __restrict__ bits)
+ * per packet; survivor words are read 16 steps (8 uint4, coalesced across the warp) at a time and
+ * the decoded bits leave as one 32-bit word per 32 steps, bit i = decoded bit 32j+i.  64 registers, so
+ * 32 one-warp blocks fit on an SM and a two-wave Viterbi batch is a single traceback wave. */
+__global__ void __launch_bounds__(32, 32) traceback_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
+                                                           const w80211_desc* __restrict__ desc, const uint2* __restrict__ surv,
+                                                           uint32_t* __restrict__ bits)
 {
     const int g = blockIdx.x, lane = threadIdx.x;
     const int4 G = grp[g];
@@ -312,29 +313,33 @@ __global__ void __launch_bounds__(32) traceback_kernel(const int4* __restrict__ 
     const uint4* s4 = reinterpret_cast<const uint4*>(surv + (size_t)G.x * 32) + lane;
     uint32_t* out = bits + (size_t)G.z * 32 + lane;
     int st = 0;
-    for (int j = (T - 1) >> 5; j >= 0; j--) {
-        uint4 w[16];
-        const int t0 = j << 5;
+    uint32_t word = 0;
+    for (int c = (T - 1) >> 4; c >= 0; c--) { /* chunk c = steps 16c .. 16c+15 */
+        uint4 w[8];
+        const int t0 = c << 4;
 #pragma unroll
-        for (int k = 0; k < 16; k++) {
+        for (int k = 0; k < 8; k++) {
             if (t0 + 2 * k < T) w[k] = __ldg(s4 + (size_t)((t0 >> 1) + k) * 32);
         }
-        uint32_t word = 0;
+        const int sh = (c & 1) << 4;
 #pragma unroll
-        for (int k = 15; k >= 0; k--) {
+        for (int k = 7; k >= 0; k--) {
             /* step t0+2k+1 (z,w) then t0+2k (x,y) */
             if (t0 + 2 * k + 1 < T) {
                 uint32_t sel = (st & 32) ? w[k].w : w[k].z;
-                word |= (uint32_t)(st >> 5) << (2 * k + 1);
+                word |= (uint32_t)(st >> 5) << (sh + 2 * k + 1);
                 st = ((st & 31) << 1) | ((sel >> (st & 31)) & 1u);
             }
             if (t0 + 2 * k < T) {
                 uint32_t sel = (st & 32) ? w[k].y : w[k].x;
-                word |= (uint32_t)(st >> 5) << (2 * k);
+                word |= (uint32_t)(st >> 5) << (sh + 2 * k);
                 st = ((st & 31) << 1) | ((sel >> (st & 31)) & 1u);
             }
         }
-        out[(size_t)j * 32] = word;
+        if (!(c & 1)) {
+            out[(size_t)(c >> 1) * 32] = word;
+            word = 0;
+        }
     }
 }
 
