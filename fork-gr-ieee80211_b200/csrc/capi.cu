@@ -64,6 +64,12 @@ struct Slot {
     float host_plan_ms = 0.f;
 };
 
+/* buffers of the signal stage (w80211_signal_batch) */
+struct SigStage {
+    DevBuf iq[2], syncs, res, chan_all, acc, out_iq[2], out_chan;
+    PinBuf h_res, h_acc;
+};
+
 } // namespace
 
 struct w80211_ctx {
@@ -71,6 +77,7 @@ struct w80211_ctx {
     int nslots = 2;
     W80211Tables* d_tab = nullptr;
     Slot slots[4];
+    SigStage sig;
     w80211_stats stats = {};
     std::string err;
 };
@@ -544,6 +551,9 @@ size_t w80211_sizeof(int what)
     case 5: return sizeof(w80211_stats);
     case 6: return sizeof(w80211_timing);
     case 7: return sizeof(w80211_cfg);
+    case 8: return sizeof(w80211_sync);
+    case 9: return sizeof(w80211_signal_in);
+    case 10: return sizeof(w80211_signal_out);
     default: return 0;
     }
 }
@@ -600,6 +610,14 @@ void w80211_destroy(w80211_ctx* ctx)
         for (int e = 0; e < EV_COUNT; e++)
             if (s.ev[e]) cudaEventDestroy(s.ev[e]);
         if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    {
+        SigStage& g = ctx->sig;
+        DevBuf* db[] = {&g.iq[0], &g.iq[1], &g.syncs, &g.res, &g.chan_all, &g.acc, &g.out_iq[0], &g.out_iq[1], &g.out_chan};
+        for (DevBuf* b : db)
+            if (b->p) cudaFree(b->p);
+        if (g.h_res.p) cudaFreeHost(g.h_res.p);
+        if (g.h_acc.p) cudaFreeHost(g.h_acc.p);
     }
     if (ctx->d_tab) cudaFree(ctx->d_tab);
     delete ctx;
@@ -670,6 +688,141 @@ int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out
     int r = w80211_rx_submit(ctx, 0, in, out);
     if (r < 0) return r;
     return w80211_rx_collect(ctx, 0);
+}
+
+int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_signal_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (!in || !out || in->nsync < 0 || (in->nant != 1 && in->nant != 2) || (in->nsync > 0 && !in->syncs) ||
+        (in->nsamples > 0 && (!in->iq[0] || (in->nant == 2 && !in->iq[1]))) || in->start > in->nsamples)
+        return fail(ctx, W80211_E_ARG, "bad signal_batch arguments");
+    if (in->nsync > 0 && (!out->pkts || !out->chan)) return fail(ctx, W80211_E_ARG, "signal_batch: pkts / chan missing");
+    Slot& s = ctx->slots[0];
+    if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = s.stream;
+    SigStage& g = ctx->sig;
+    const int ns = in->nsync, nant = in->nant;
+    out->npkt = out->nsync_used = out->n_rejected = 0;
+    out->iq_used = 0;
+    out->next = in->start;
+    for (int i = 1; i < ns; i++)
+        if (in->syncs[i].pos < in->syncs[i - 1].pos) return fail(ctx, W80211_E_ARG, "signal_batch: syncs not in ascending order");
+    if (ns == 0) {
+        out->next = in->nsamples;
+        return W80211_OK;
+    }
+    /* raw samples */
+    const float2* raw[2] = {nullptr, nullptr};
+    for (int a = 0; a < nant; a++) {
+        if (in->mem == W80211_MEM_DEVICE) {
+            raw[a] = (const float2*)in->iq[a];
+        } else {
+            RS(dev_reserve(ctx, g.iq[a], (size_t)in->nsamples * 8 + 64));
+            CK(cudaMemcpyAsync(g.iq[a].p, in->iq[a], (size_t)in->nsamples * 8, cudaMemcpyHostToDevice, st));
+            raw[a] = (const float2*)g.iq[a].p;
+        }
+    }
+    /* every flag's L-SIG at once */
+    RS(dev_reserve(ctx, g.syncs, (size_t)ns * sizeof(w80211_sync)));
+    RS(dev_reserve(ctx, g.res, (size_t)ns * sizeof(int4)));
+    RS(dev_reserve(ctx, g.chan_all, (size_t)ns * 64 * 8));
+    RS(pin_reserve(ctx, g.h_res, (size_t)ns * sizeof(int4)));
+    CK(cudaMemcpyAsync(g.syncs.p, in->syncs, (size_t)ns * sizeof(w80211_sync), cudaMemcpyHostToDevice, st));
+    w_launch_lsig(st, ctx->d_tab, ns, (const w80211_sync*)g.syncs.p, raw[0], in->nsamples, (int4*)g.res.p, (float2*)g.chan_all.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(g.h_res.p, g.res.p, (size_t)ns * sizeof(int4), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    /* the block's state machine over the flags, in stream order (signal_impl.cc:76-160,194-201) */
+    const int4* hr = (const int4*)g.h_res.p;
+    RS(pin_reserve(ctx, g.h_acc, (size_t)ns * sizeof(w_sig_acc)));
+    w_sig_acc* acc = (w_sig_acc*)g.h_acc.p;
+    uint64_t resume = in->start, used = 0;
+    int np = 0, max_nsamp = 0, i = 0;
+    bool stopped = false;
+    for (; i < ns; i++) {
+        const w80211_sync& sy = in->syncs[i];
+        if (sy.pos < resume) continue; /* consumed inside a packet / the 80 samples after a failed check */
+        if (!(sy.flags & W80211_SYNC_TAGGED)) {
+            resume = sy.pos + 1;
+            continue;
+        }
+        if (sy.pos + 224 > in->nsamples) {
+            stopped = true;
+            break;
+        }
+        if (hr[i].x != 1) {
+            out->n_rejected++;
+            resume = sy.pos + 80;
+            continue;
+        }
+        const int nsamp = hr[i].w;
+        if (sy.pos + 224 + (uint64_t)nsamp > in->nsamples) {
+            stopped = true;
+            break;
+        }
+        if (used + (uint64_t)nsamp > out->iq_capacity)
+            return fail(ctx, W80211_E_ARG, "signal_batch: iq_capacity %llu too small", (unsigned long long)out->iq_capacity);
+        w80211_pkt_in& pk = out->pkts[np];
+        pk.iq_offset = used;
+        pk.nsamp = nsamp;
+        pk.l_mcs = hr[i].y;
+        pk.l_len = hr[i].z;
+        pk.cfo = sy.rad * 3183098.8618379068f; /* rad * 20e6 / 2pi, binary32 like signal_impl.cc:136 */
+        pk.snr = sy.snr;
+        pk.rssi = sy.rssi;
+        pk.iq_scale = 1.0f;
+        if (out->sync_of_pkt) out->sync_of_pkt[np] = i;
+        acc[np].src = sy.pos;
+        acc[np].dst = used;
+        acc[np].nsamp = nsamp;
+        acc[np].rad = sy.rad;
+        acc[np].sync = i;
+        acc[np].pad_ = 0;
+        max_nsamp = std::max(max_nsamp, nsamp);
+        used += (uint64_t)nsamp;
+        np++;
+        resume = sy.pos + 224 + (uint64_t)nsamp;
+    }
+    out->npkt = np;
+    out->iq_used = used;
+    if (stopped && !in->final) {
+        out->nsync_used = i;
+        out->next = in->syncs[i].pos;
+    } else {
+        out->nsync_used = ns;
+        out->next = in->nsamples;
+    }
+    if (np == 0) return W80211_OK;
+    /* copy the accepted packets with their rotation */
+    for (int a = 0; a < nant; a++)
+        if (!out->iq[a]) return fail(ctx, W80211_E_ARG, "signal_batch: output iq[%d] missing", a);
+    float2* dst[2] = {nullptr, nullptr};
+    float2* dchan = nullptr;
+    if (out->mem == W80211_MEM_DEVICE) {
+        dst[0] = (float2*)out->iq[0];
+        dst[1] = (float2*)out->iq[1];
+        dchan = (float2*)out->chan;
+    } else {
+        for (int a = 0; a < nant; a++) {
+            RS(dev_reserve(ctx, g.out_iq[a], (size_t)used * 8 + 64));
+            dst[a] = (float2*)g.out_iq[a].p;
+        }
+        RS(dev_reserve(ctx, g.out_chan, (size_t)np * 64 * 8));
+        dchan = (float2*)g.out_chan.p;
+    }
+    RS(dev_reserve(ctx, g.acc, (size_t)np * sizeof(w_sig_acc)));
+    CK(cudaMemcpyAsync(g.acc.p, acc, (size_t)np * sizeof(w_sig_acc), cudaMemcpyHostToDevice, st));
+    w_launch_cfo_copy(st, np, nant, max_nsamp, (const w_sig_acc*)g.acc.p, raw[0], raw[1], dst[0], dst[1],
+                      (const float2*)g.chan_all.p, dchan);
+    CK(cudaGetLastError());
+    if (out->mem != W80211_MEM_DEVICE) {
+        for (int a = 0; a < nant; a++) CK(cudaMemcpyAsync(out->iq[a], dst[a], (size_t)used * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(out->chan, dchan, (size_t)np * 64 * 8, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    ctx->stats.kernel_launches += 2;
+    return W80211_OK;
 }
 
 int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out)

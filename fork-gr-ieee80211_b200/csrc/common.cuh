@@ -121,6 +121,8 @@ __device__ __forceinline__ void fft64_twiddles(int g, float* wr, float* wi)
         wi[k1] = C8_W64_IM[(g * k1) & 63];
     }
 }
+/* same, with lane g's inputs x[8*n1+g] already in (re[n1], im[n1]) */
+__device__ __forceinline__ void fft64_lane8_regs(int g, float2* xch, float* re, float* im, const float* wr, const float* wi);
 __device__ __forceinline__ void fft64_lane8(const float2* __restrict__ src, int g, float2* xch, float* re, float* im,
                                             const float* wr, const float* wi, bool valid)
 {
@@ -130,6 +132,10 @@ __device__ __forceinline__ void fft64_lane8(const float2* __restrict__ src, int 
         re[n1] = v.x;
         im[n1] = v.y;
     }
+    fft64_lane8_regs(g, xch, re, im, wr, wi);
+}
+__device__ __forceinline__ void fft64_lane8_regs(int g, float2* xch, float* re, float* im, const float* wr, const float* wi)
+{
     c8_fft8(re, im);
     if (g) { /* n2*k1 == 0 is left untouched, as in c8_fft64() */
 #pragma unroll
@@ -170,6 +176,19 @@ void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nan
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nsymtot, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* sym_prefix,
                     const float2* chan, int chan_stride, float* llr);
+/* signal stage: per-flag L-SIG result and the copy list of accepted packets */
+struct w_sig_acc {
+    unsigned long long src; /* sync position in the raw stream */
+    unsigned long long dst; /* first output sample */
+    int nsamp;
+    float rad;
+    int sync; /* row of chan_all */
+    int pad_;
+};
+void w_launch_lsig(cudaStream_t st, const W80211Tables* tab, int nsync, const w80211_sync* syncs, const float2* iq0,
+                   unsigned long long nsamples, int4* res, float2* chan_all);
+void w_launch_cfo_copy(cudaStream_t st, int npkt, int nant, int max_nsamp, const w_sig_acc* acc, const float2* in0,
+                       const float2* in1, float2* out0, float2* out1, const float2* chan_all, float2* chan_out);
 void w_launch_sc16_to_fc32(cudaStream_t st, int npkt, int nant, const w80211_pkt_in* pkts, const void* raw0, const void* raw1,
                            float2* out0, float2* out1, unsigned long long nsamples);
 int w_launch_viterbi(cudaStream_t st, const int* cr_first, const int4* grp, const int* slot_pkt, const w80211_desc* desc,

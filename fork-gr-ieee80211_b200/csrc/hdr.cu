@@ -537,3 +537,120 @@ void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nan
     if (npkt <= 0) return;
     hdr_kernel<<<npkt, 32, 0, st>>>(tab, npkt, nant, iq0, iq1, nsamples, pk, chan_in, desc, chan_out, chan_stride);
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * L-SIG of one sync flag, one warp per flag: the S_DEMOD state of the reference's signal / signal2
+ * blocks (lib/signal_impl.cc:108-160, lib/signal2_impl.cc:109-163).
+ *   rotate the two L-LTF symbols and the L-SIG symbol (offsets +8, +72, +152 from the flag) by
+ *   exp(j*(i+offset)*rad), FFT each, H = (LTF1 + LTF2) / (2*L) on the 52 legacy bins,
+ *   procLHSigDemodDeint (cloud80211phy.cc:609-627), 24-step Viterbi (:2001-2088),
+ *   signalCheckLegacy (:650-728).
+ * res[p] = (1, rate index, LENGTH, nsym*80) when the check passes, (0,..) when it fails, (-1,..) when
+ * the flag has no tags or fewer than 224 samples follow it.  chan_all[p] = the "chan" tag: H on the
+ * legacy bins, zero elsewhere (d_h starts as zeros and only those bins are ever written). */
+__global__ void __launch_bounds__(32) lsig_kernel(const W80211Tables* __restrict__ T, int nsync,
+                                                  const w80211_sync* __restrict__ syncs, const float2* __restrict__ iq0,
+                                                  unsigned long long nsamples, int4* __restrict__ res,
+                                                  float2* __restrict__ chan_all)
+{
+    __shared__ HdrSmem S;
+    const int p = blockIdx.x;
+    if (p >= nsync) return;
+    const int lane = threadIdx.x;
+    const int grp = lane >> 3, g = lane & 7;
+    const w80211_sync sy = syncs[p];
+    float2* cho = chan_all + (size_t)p * 64;
+    if (!(sy.flags & W80211_SYNC_TAGGED) || sy.pos + 224ull > nsamples) {
+        if (lane == 0) res[p] = make_int4(-1, 0, 0, 0);
+        cho[lane] = make_float2(0.f, 0.f);
+        cho[lane + 32] = make_float2(0.f, 0.f);
+        return;
+    }
+    const float2* x = iq0 + sy.pos;
+    {
+        float wr[8], wi[8], re[8], im[8];
+        fft64_twiddles(g, wr, wi);
+        const int base = grp == 0 ? 8 : (grp == 1 ? 72 : 152);
+#pragma unroll
+        for (int n1 = 0; n1 < 8; n1++) {
+            re[n1] = 0.f;
+            im[n1] = 0.f;
+            if (grp < 3) {
+                const int k = base + 8 * n1 + g;
+                const float2 v = __ldg(x + k);
+                float sn, cs;
+                sincosf(__fmul_rn((float)k, sy.rad), &sn, &cs);
+                const cf32 r = c_mul(c_make(v.x, v.y), c_make(cs, sn));
+                re[n1] = r.x;
+                im[n1] = r.y;
+            }
+        }
+        fft64_lane8_regs(g, S.xch[grp], re, im, wr, wi);
+#pragma unroll
+        for (int k2 = 0; k2 < 8; k2++) S.F[grp][g + 8 * k2] = make_float2(re[k2], im[k2]);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int i = lane + 32 * h;
+        const bool used = T->sig_demap[i] >= 0 || i == 7 || i == 21 || i == 43 || i == 57;
+        cf32 hh = c_make(0.f, 0.f);
+        if (used) {
+            /* LTF_L_26_F_FLOAT2[i] = 2 * L-LTF sign, the HT-LTF sign on the legacy bins */
+            const float l2 = __fmul_rn(2.0f, T->ltf_nl[i]);
+            hh = c_divf(c_add(c_make(S.F[0][i].x, S.F[0][i].y), c_make(S.F[1][i].x, S.F[1][i].y)), l2);
+        }
+        S.eq[0][i] = make_float2(hh.x, hh.y);
+        cho[i] = make_float2(hh.x, hh.y);
+    }
+    __syncwarp();
+    const float2* hl = S.eq[0];
+    const cf32 e7 = c_div(c_make(S.F[2][7].x, S.F[2][7].y), c_make(hl[7].x, hl[7].y));
+    const cf32 e21 = c_div(c_make(S.F[2][21].x, S.F[2][21].y), c_make(hl[21].x, hl[21].y));
+    const cf32 e43 = c_div(c_make(S.F[2][43].x, S.F[2][43].y), c_make(hl[43].x, hl[43].y));
+    const cf32 e57 = c_div(c_make(S.F[2][57].x, S.F[2][57].y), c_make(hl[57].x, hl[57].y));
+    const cf32 ps = c_conj(c_add(c_add(c_sub(e7, e21), e43), e57));
+    const float pa = c_abs(ps);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int i = lane + 32 * h;
+        const int dm = T->sig_demap[i];
+        if (dm >= 0) {
+            const cf32 m = c_divf(c_mul(c_div(c_make(S.F[2][i].x, S.F[2][i].y), c_make(hl[i].x, hl[i].y)), ps), pa);
+            S.llr[0][dm] = m.x;
+        }
+    }
+    __syncwarp();
+    sig_viterbi(S, S.llr[0], 24, lane);
+    if (lane == 0) {
+        const uint8_t* b = S.bits;
+        int par = 0;
+        for (int i = 0; i < 17; i++) par += b[i];
+        const int rate = bits_le(b, 0, 4);
+        const int len = bits_le(b, 5, 12);
+        bool ok = b[3] == 1 && b[4] == 0 && ((par & 1) ^ b[17]) == 0 && len >= 14 && len <= 4095;
+        /* RATE field (bit 0 first) -> rate index; unknown patterns fall back to 0 like the reference's default case */
+        int mcs = 0;
+        switch (rate) {
+        case 11: mcs = 0; break;
+        case 15: mcs = 1; break;
+        case 10: mcs = 2; break;
+        case 14: mcs = 3; break;
+        case 9: mcs = 4; break;
+        case 13: mcs = 5; break;
+        case 8: mcs = 6; break;
+        case 12: mcs = 7; break;
+        default: mcs = 0; break;
+        }
+        const int nd[8] = {24, 36, 48, 72, 96, 144, 192, 216};
+        const int nsym = (len * 8 + 22 + nd[mcs] - 1) / nd[mcs];
+        res[p] = ok ? make_int4(1, mcs, len, nsym * 80) : make_int4(0, 0, 0, 0);
+    }
+}
+
+void w_launch_lsig(cudaStream_t st, const W80211Tables* tab, int nsync, const w80211_sync* syncs, const float2* iq0,
+                   unsigned long long nsamples, int4* res, float2* chan_all)
+{
+    if (nsync <= 0) return;
+    lsig_kernel<<<nsync, 32, 0, st>>>(tab, nsync, syncs, iq0, nsamples, res, chan_all);
+}

@@ -34,3 +34,44 @@ void w_launch_sc16_to_fc32(cudaStream_t st, int npkt, int nant, const w80211_pkt
     if (npkt <= 0) return;
     sc16_to_fc32_kernel<<<npkt, 256, 0, st>>>(npkt, nant, pkts, (const short2*)raw0, (const short2*)raw1, out0, out1, nsamples);
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * S_COPY of the reference's signal / signal2 blocks (lib/signal_impl.cc:164-191, signal2_impl.cc:167-199):
+ * sample k of an accepted packet = raw[sync + 224 + k] * (cosf(t), sinf(t)), t = (float)(k + 224) * rad,
+ * on every antenna; plus the packet's "chan" tag copied from the per-flag table.  16 bytes of HBM traffic per
+ * sample and antenna; blockIdx.y walks the packet in chunks so that long and short packets share one grid. */
+#define CFO_CHUNK 2048
+__global__ void __launch_bounds__(256) cfo_copy_kernel(int npkt, int nant, const w_sig_acc* __restrict__ acc,
+                                                       const float2* __restrict__ in0, const float2* __restrict__ in1,
+                                                       float2* __restrict__ out0, float2* __restrict__ out1,
+                                                       const float2* __restrict__ chan_all, float2* __restrict__ chan_out)
+{
+    const int p = blockIdx.x;
+    if (p >= npkt) return;
+    const w_sig_acc a = acc[p];
+    const int k0 = blockIdx.y * CFO_CHUNK;
+    if (blockIdx.y == 0 && threadIdx.x < 64) chan_out[(size_t)p * 64 + threadIdx.x] = chan_all[(size_t)a.sync * 64 + threadIdx.x];
+    if (k0 >= a.nsamp) return;
+    const int k1 = min(a.nsamp, k0 + CFO_CHUNK);
+    for (int k = k0 + threadIdx.x; k < k1; k += blockDim.x) {
+        float sn, cs;
+        sincosf(__fmul_rn((float)(k + 224), a.rad), &sn, &cs);
+        const cf32 w = c_make(cs, sn);
+        const float2 v = __ldg(in0 + a.src + 224 + k);
+        const cf32 r = c_mul(c_make(v.x, v.y), w);
+        out0[a.dst + k] = make_float2(r.x, r.y);
+        if (nant == 2) {
+            const float2 v1 = __ldg(in1 + a.src + 224 + k);
+            const cf32 r1 = c_mul(c_make(v1.x, v1.y), w);
+            out1[a.dst + k] = make_float2(r1.x, r1.y);
+        }
+    }
+}
+
+void w_launch_cfo_copy(cudaStream_t st, int npkt, int nant, int max_nsamp, const w_sig_acc* acc, const float2* in0,
+                       const float2* in1, float2* out0, float2* out1, const float2* chan_all, float2* chan_out)
+{
+    if (npkt <= 0) return;
+    dim3 grid(npkt, max(1, (max_nsamp + CFO_CHUNK - 1) / CFO_CHUNK));
+    cfo_copy_kernel<<<grid, 256, 0, st>>>(npkt, nant, acc, in0, in1, out0, out1, chan_all, chan_out);
+}

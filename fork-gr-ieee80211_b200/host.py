@@ -19,7 +19,7 @@ F_L, F_HT, F_VHT = 0, 1, 2
 SYMBOLS = [
     "w80211_abi_version", "w80211_sizeof", "w80211_create", "w80211_destroy", "w80211_last_error", "w80211_stats_get",
     "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
-    "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free",
+    "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free", "w80211_signal_batch",
 ]
 
 
@@ -58,6 +58,21 @@ class BatchOut(C.Structure):
                 ("mpdu_capacity", C.c_uint32), ("llr", C.c_void_p), ("llr_capacity", C.c_uint64),
                 ("n_mpdu", C.c_uint32), ("n_crc_ok", C.c_uint32), ("n_bytes", C.c_uint64), ("n_llr", C.c_uint64),
                 ("psdu_bits_ok", C.c_uint64)]
+
+
+SYNC_TAGGED = 1
+SYNC_DTYPE = np.dtype([("pos", "<u8"), ("rad", "<f4"), ("snr", "<f4"), ("rssi", "<f4"), ("flags", "<i4")], align=True)
+
+
+class SignalIn(C.Structure):
+    _fields_ = [("nsync", C.c_int32), ("nant", C.c_int32), ("mem", C.c_int32), ("final", C.c_int32),
+                ("iq", C.c_void_p * 2), ("nsamples", C.c_uint64), ("syncs", C.c_void_p), ("start", C.c_uint64)]
+
+
+class SignalOut(C.Structure):
+    _fields_ = [("mem", C.c_int32), ("npkt", C.c_int32), ("nsync_used", C.c_int32), ("n_rejected", C.c_int32),
+                ("next", C.c_uint64), ("iq_capacity", C.c_uint64), ("iq_used", C.c_uint64), ("pkts", C.c_void_p),
+                ("sync_of_pkt", C.c_void_p), ("chan", C.c_void_p), ("iq", C.c_void_p * 2)]
 
 
 class Stats(C.Structure):
@@ -102,6 +117,7 @@ def load():
         L.w80211_rx_submit.argtypes = [vp, C.c_int, C.POINTER(BatchIn), C.POINTER(BatchOut)]
         L.w80211_rx_collect.argtypes = [vp, C.c_int]
         L.w80211_rx_batch.argtypes = [vp, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+        L.w80211_signal_batch.argtypes = [vp, C.POINTER(SignalIn), C.POINTER(SignalOut)]
         _lib = L
     return _lib
 
@@ -291,6 +307,43 @@ class Receiver:
         self._check(self.L.w80211_decode_batch(self.h, npkt, desc.ctypes.data, llr.ctypes.data, llr.size, MEM_HOST,
                                                C.byref(bo)))
         return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo)
+
+    def signal(self, raw, pos, rad=0.0, snr=0.0, rssi=0.0, start=0, final=True, tagged=None):
+        """Raw samples + sync flags -> packets in demod's input format (w80211_signal_batch): what signal / signal2 do.
+        raw: list of 1 or 2 complex64 arrays; pos: flag positions (ascending); rad/snr/rssi: scalars or per-flag arrays.
+        Returns dict(iq=[per antenna], pkts, chan, sync_of_pkt, next, nsync_used, n_rejected)."""
+        raw = [np.ascontiguousarray(x, np.complex64) for x in raw]
+        pos = np.atleast_1d(np.asarray(pos, np.uint64))
+        sy = np.zeros(len(pos), SYNC_DTYPE)
+        sy["pos"] = pos
+        sy["rad"] = rad
+        sy["snr"] = snr
+        sy["rssi"] = rssi
+        sy["flags"] = SYNC_TAGGED if tagged is None else np.where(np.asarray(tagged), SYNC_TAGGED, 0)
+        n = len(raw[0])
+        si = SignalIn()
+        si.nsync, si.nant, si.mem, si.final = len(sy), len(raw), MEM_HOST, int(bool(final))
+        for a, x in enumerate(raw):
+            assert len(x) == n
+            si.iq[a] = x.ctypes.data
+        si.nsamples = n
+        si.syncs = sy.ctypes.data
+        si.start = int(start)
+        so = SignalOut()
+        cap = max(len(sy), 1)
+        pk = np.zeros(cap, PKT_IN_DTYPE)
+        sop = np.zeros(cap, np.int32)
+        ch = np.zeros((cap, 64), np.complex64)
+        out = [np.zeros(max(n, 1), np.complex64) for _ in raw]
+        so.mem = MEM_HOST
+        so.iq_capacity = n
+        so.pkts, so.sync_of_pkt, so.chan = pk.ctypes.data, sop.ctypes.data, ch.ctypes.data
+        for a, x in enumerate(out):
+            so.iq[a] = x.ctypes.data
+        self._check(self.L.w80211_signal_batch(self.h, C.byref(si), C.byref(so)))
+        k, used = so.npkt, so.iq_used
+        return {"iq": [x[:used] for x in out], "pkts": pk[:k].copy(), "chan": ch[:k].copy(), "sync_of_pkt": sop[:k].copy(),
+                "next": int(so.next), "nsync_used": int(so.nsync_used), "n_rejected": int(so.n_rejected)}
 
     def stats(self):
         s = Stats()

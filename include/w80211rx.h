@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define W80211_ABI_VERSION 2
+#define W80211_ABI_VERSION 3
 
 /* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
 #define W80211_F_L 0
@@ -157,6 +157,42 @@ typedef struct w80211_stats {
     uint64_t kernel_launches;
 } w80211_stats;
 
+/* ---- the front half: signal / signal2 ------------------------------------------
+ * One sync flag of the reference's sync block: a non-zero item on signal's input 0 with the tags
+ * "rad", "snr", "rssi" (lib/signal_impl.cc:80-98). */
+#define W80211_SYNC_TAGGED 1 /* flags: the item carries tags; a flag without tags is skipped (signal_impl.cc:100-104) */
+typedef struct w80211_sync {
+    uint64_t pos;    /* index of the flagged sample ("L-LTF start + 16") in iq[] */
+    float rad;       /* tag "rad": carrier frequency offset in radians per sample */
+    float snr, rssi; /* tags "snr", "rssi": carried through */
+    int32_t flags;   /* W80211_SYNC_TAGGED */
+} w80211_sync;
+
+typedef struct w80211_signal_in {
+    int32_t nsync;
+    int32_t nant;            /* 1: signal (lib/signal_impl.cc), 2: signal2 (lib/signal2_impl.cc; L-SIG from antenna 1) */
+    int32_t mem;             /* where iq[] lives; syncs is always host memory */
+    int32_t final;           /* non-zero: no samples follow this buffer, a packet cut off by its end is dropped */
+    const float* iq[2];      /* raw received samples, interleaved (re,im) binary32 */
+    uint64_t nsamples;       /* complex samples per antenna */
+    const w80211_sync* syncs; /* [nsync], ascending pos */
+    uint64_t start;          /* the trigger search begins here (0, or what the previous buffer left over) */
+} w80211_signal_in;
+
+typedef struct w80211_signal_out {
+    int32_t mem;             /* where iq[] and chan are written: a MEM_DEVICE result feeds w80211_rx_submit directly */
+    int32_t npkt;            /* out: packets whose L-SIG passed signalCheckLegacy and that lie wholly inside the buffer */
+    int32_t nsync_used;      /* out: leading entries of syncs[] that were settled (accepted, rejected, skipped or overlapped) */
+    int32_t n_rejected;      /* out: flags whose L-SIG failed the check (the reference resumes 80 samples later) */
+    uint64_t next;           /* out: where the reference's state machine stands: first sample the next call must still see */
+    uint64_t iq_capacity;    /* complex samples per antenna iq[] can hold */
+    uint64_t iq_used;        /* out */
+    w80211_pkt_in* pkts;     /* host [>= nsync]: iq_offset into iq[], nsamp, l_mcs, l_len, cfo = rad * 20e6 / 2pi, snr, rssi */
+    int32_t* sync_of_pkt;    /* host [>= nsync] or NULL: index into syncs[] of each packet */
+    float* chan;             /* [>= nsync][64][2]: tag "chan" (signal_impl.cc:143) */
+    float* iq[2];            /* CFO-corrected samples after L-SIG, nsamp per packet, packets back to back (no pad items) */
+} w80211_signal_out;
+
 /* Timing of the last completed batch, measured with CUDA events on the ctx's own stream (ms). */
 typedef struct w80211_timing {
     float h2d, header, demod, viterbi, traceback, post, d2h, total;
@@ -166,7 +202,8 @@ typedef struct w80211_timing {
 } w80211_timing;
 
 int w80211_abi_version(void);
-/* sizeof of the ABI structs as compiled: 0 pkt_in, 1 batch_in, 2 desc, 3 mpdu, 4 batch_out, 5 stats, 6 timing, 7 cfg
+/* sizeof of the ABI structs as compiled: 0 pkt_in, 1 batch_in, 2 desc, 3 mpdu, 4 batch_out, 5 stats, 6 timing, 7 cfg,
+ * 8 sync, 9 signal_in, 10 signal_out
  * (lets a binding written in another language check its own layout) */
 size_t w80211_sizeof(int what);
 int w80211_create(const w80211_cfg* cfg, w80211_ctx** out);
@@ -181,6 +218,15 @@ void* w80211_stream(const w80211_ctx* ctx, int slot);
  * full-speed DMA without linking the CUDA runtime itself.  NULL when the allocation fails. */
 void* w80211_host_alloc(size_t bytes);
 void w80211_host_free(void* p);
+
+/* Raw samples + sync flags -> packets in demod's input format: what signal / signal2 do between sync and demod
+ * (lib/signal_impl.cc:62-212, lib/signal2_impl.cc:62-222).  Every flag's L-SIG is demodulated and decoded in
+ * parallel (CFO rotation, 3 FFTs, procLHSigDemodDeint cloud80211phy.cc:609-627, 24-step Viterbi, signalCheckLegacy
+ * :650-728); the host then walks the flags in order the way the block's TRIGGER/DEMOD/COPY states would (a flag
+ * inside an accepted packet, or within 80 samples after a rejected one, is never looked at) and a second kernel
+ * copies the accepted packets with the per-sample rotation of signal_impl.cc:172-176.  Synchronous, uses slot 0.
+ * The rotation uses cosf/sinf: results agree with a host libm to 1 ulp of the factor, not bit for bit. */
+int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_signal_out* out);
 
 /* IQ -> LLR stream + descriptors: what demod / demod2 write to their output port.
  * out->desc and out->llr are filled; nothing is decoded.  Synchronous. */

@@ -276,6 +276,7 @@ int ref_table(const char* name, double* out, int maxn)
     else if (k == "mapDeintVhtSigB20") { ip = mapDeintVhtSigB20; n = 52; }
     else if (k == "LTF_NL_28_F_FLOAT") { fp = LTF_NL_28_F_FLOAT; n = 64; }
     else if (k == "LTF_NL_28_F_FLOAT2") { fp = LTF_NL_28_F_FLOAT2; n = 64; }
+    else if (k == "LTF_L_26_F_FLOAT") { fp = LTF_L_26_F_FLOAT; n = 64; }
     else if (k == "PILOT_P") { fp = PILOT_P; n = 127; }
     if (n > maxn) n = maxn;
     for (int i = 0; i < n; i++) out[i] = ip ? (double)ip[i] : (double)fp[i];
