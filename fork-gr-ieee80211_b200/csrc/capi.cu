@@ -706,6 +706,7 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
     out->npkt = out->nsync_used = out->n_rejected = 0;
     out->iq_used = 0;
     out->next = in->start;
+    out->need = 0;
     for (int i = 1; i < ns; i++)
         if (in->syncs[i].pos < in->syncs[i - 1].pos) return fail(ctx, W80211_E_ARG, "signal_batch: syncs not in ascending order");
     if (ns == 0) {
@@ -737,7 +738,7 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
     const int4* hr = (const int4*)g.h_res.p;
     RS(pin_reserve(ctx, g.h_acc, (size_t)ns * sizeof(w_sig_acc)));
     w_sig_acc* acc = (w_sig_acc*)g.h_acc.p;
-    uint64_t resume = in->start, used = 0;
+    uint64_t resume = in->start, used = 0, need = 0;
     int np = 0, max_nsamp = 0, i = 0;
     bool stopped = false;
     for (; i < ns; i++) {
@@ -749,6 +750,7 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
         }
         if (sy.pos + 224 > in->nsamples) {
             stopped = true;
+            need = sy.pos + 224;
             break;
         }
         if (hr[i].x != 1) {
@@ -759,6 +761,7 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
         const int nsamp = hr[i].w;
         if (sy.pos + 224 + (uint64_t)nsamp > in->nsamples) {
             stopped = true;
+            need = sy.pos + 224 + (uint64_t)nsamp;
             break;
         }
         if (used + (uint64_t)nsamp > out->iq_capacity)
@@ -789,6 +792,7 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
     if (stopped && !in->final) {
         out->nsync_used = i;
         out->next = in->syncs[i].pos;
+        out->need = need;
     } else {
         out->nsync_used = ns;
         out->next = in->nsamples;

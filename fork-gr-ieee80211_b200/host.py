@@ -71,7 +71,7 @@ class SignalIn(C.Structure):
 
 class SignalOut(C.Structure):
     _fields_ = [("mem", C.c_int32), ("npkt", C.c_int32), ("nsync_used", C.c_int32), ("n_rejected", C.c_int32),
-                ("next", C.c_uint64), ("iq_capacity", C.c_uint64), ("iq_used", C.c_uint64), ("pkts", C.c_void_p),
+                ("next", C.c_uint64), ("need", C.c_uint64), ("iq_capacity", C.c_uint64), ("iq_used", C.c_uint64), ("pkts", C.c_void_p),
                 ("sync_of_pkt", C.c_void_p), ("chan", C.c_void_p), ("iq", C.c_void_p * 2)]
 
 
@@ -343,7 +343,7 @@ class Receiver:
         self._check(self.L.w80211_signal_batch(self.h, C.byref(si), C.byref(so)))
         k, used = so.npkt, so.iq_used
         return {"iq": [x[:used] for x in out], "pkts": pk[:k].copy(), "chan": ch[:k].copy(), "sync_of_pkt": sop[:k].copy(),
-                "next": int(so.next), "nsync_used": int(so.nsync_used), "n_rejected": int(so.n_rejected)}
+                "next": int(so.next), "need": int(so.need), "nsync_used": int(so.nsync_used), "n_rejected": int(so.n_rejected)}
 
     def stats(self):
         s = Stats()

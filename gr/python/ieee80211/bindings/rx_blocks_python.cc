@@ -1,5 +1,5 @@
-/* pybind11 bindings of the three GPU-backed blocks: python classes ieee80211.demod(mupos, mugid),
- * ieee80211.demod2() and ieee80211.decode(ifdebug), deriving gr::block / gr::basic_block exactly as the
+/* pybind11 bindings of the GPU-backed blocks: python classes ieee80211.signal(), ieee80211.signal2(),
+ * ieee80211.demod(mupos, mugid), ieee80211.demod2() and ieee80211.decode(ifdebug), deriving gr::block / gr::basic_block exactly as the
  * reference's bindings do (python/ieee80211/bindings/{demod,demod2,decode}_python.cc:36-43), so
  * `from gnuradio import ieee80211` keeps working for rx.grc / rx2.grc.
  *
@@ -11,8 +11,24 @@
 #include <gnuradio/ieee80211/decode.h>
 #include <gnuradio/ieee80211/demod.h>
 #include <gnuradio/ieee80211/demod2.h>
+#include <gnuradio/ieee80211/signal.h>
+#include <gnuradio/ieee80211/signal2.h>
 
 namespace py = pybind11;
+
+void bind_signal(py::module& m)
+{
+    using blk = ::gr::ieee80211::signal;
+    py::class_<blk, gr::block, gr::basic_block, std::shared_ptr<blk>>(m, "signal", "802.11 legacy signal field and CFO correction (B200)")
+        .def(py::init(&blk::make));
+}
+
+void bind_signal2(py::module& m)
+{
+    using blk = ::gr::ieee80211::signal2;
+    py::class_<blk, gr::block, gr::basic_block, std::shared_ptr<blk>>(m, "signal2", "802.11 legacy signal field and CFO correction, two antennas (B200)")
+        .def(py::init(&blk::make));
+}
 
 void bind_demod(py::module& m)
 {

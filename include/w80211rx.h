@@ -185,6 +185,8 @@ typedef struct w80211_signal_out {
     int32_t nsync_used;      /* out: leading entries of syncs[] that were settled (accepted, rejected, skipped or overlapped) */
     int32_t n_rejected;      /* out: flags whose L-SIG failed the check (the reference resumes 80 samples later) */
     uint64_t next;           /* out: where the reference's state machine stands: first sample the next call must still see */
+    uint64_t need;           /* out: buffer length (from sample 0 of this buffer) at which the flag at `next` can be settled;
+                                0 when nothing is pending */
     uint64_t iq_capacity;    /* complex samples per antenna iq[] can hold */
     uint64_t iq_used;        /* out */
     w80211_pkt_in* pkts;     /* host [>= nsync]: iq_offset into iq[], nsamp, l_mcs, l_len, cfo = rad * 20e6 / 2pi, snr, rssi */

@@ -21,9 +21,9 @@
 #include <gnuradio/ieee80211/decode.h>
 #include <gnuradio/ieee80211/demod.h>
 #include <gnuradio/ieee80211/demod2.h>
-#ifndef W80211_DRIVER_OURS
 #include <gnuradio/ieee80211/signal.h>
 #include <gnuradio/ieee80211/signal2.h>
+#ifndef W80211_DRIVER_OURS
 #include "cloud80211phy.h"
 #endif
 #include "mock_scheduler.h"
@@ -107,14 +107,11 @@ ref_block* ref_block_new(const char* kind, int a0, int a1)
 {
     ref_block* b = new ref_block;
     std::string k(kind);
-#ifndef W80211_DRIVER_OURS
     if (k == "signal")
         b->blk = gr::ieee80211::signal::make();
     else if (k == "signal2")
         b->blk = gr::ieee80211::signal2::make();
-    else
-#endif
-    if (k == "demod")
+    else if (k == "demod")
         b->blk = gr::ieee80211::demod::make(a0, a1);
     else if (k == "demod2")
         b->blk = gr::ieee80211::demod2::make();

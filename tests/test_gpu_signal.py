@@ -9,40 +9,13 @@ import numpy as np
 import pytest
 
 import w80211rx
-from util import llr_close, TAG_KEYS
+from util import llr_close, TAG_KEYS, build_stream
 
 gp = w80211rx.gen_ppdu
 g = w80211rx.gen
 host = w80211rx.host
 
 pytestmark = pytest.mark.gpu
-
-
-def build_stream(batches, rads, gap=300, seed=0, noise=1e-3):
-    """Concatenate the raw PPDUs of gen_batch() dicts into one stream per antenna, every packet with its own carrier
-    offset (rad per sample), separated by `gap` samples of noise.  -> (raw list, flag positions, rad per flag)"""
-    rng = np.random.default_rng(seed)
-    nant = batches[0]["nrx"]
-    parts = [[] for _ in range(nant)]
-    pos, rr = [], []
-    off = 0
-    k = 0
-    for b in batches:
-        npkt, n = b["ppdu"][0].shape
-        for p in range(npkt):
-            rad = float(rads[k % len(rads)])
-            k += 1
-            lead = (rng.standard_normal((nant, gap)) + 1j * rng.standard_normal((nant, gap))) * noise
-            rot = np.exp(-1j * rad * np.arange(n))
-            for a in range(nant):
-                parts[a].append(lead[a].astype(np.complex64))
-                parts[a].append((b["ppdu"][a][p].astype(np.complex128) * rot).astype(np.complex64))
-            pos.append(off + gap + b["sync_idx"])
-            rr.append(rad)
-            off += gap + n
-    tail = np.zeros(400, np.complex64)
-    raw = [np.concatenate(x + [tail]) for x in parts]
-    return raw, np.array(pos, np.int64), np.array(rr, np.float32)
 
 
 def ref_signal(refgr, raw, pos, rad, snr=17.5, rssi=-42.0):

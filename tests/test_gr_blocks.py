@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 import w80211rx
-from util import ref_chain
+from util import ref_chain, build_stream
 
 gp, g, host = w80211rx.gen_ppdu, w80211rx.gen, w80211rx.host
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -145,3 +145,51 @@ def test_blocks_without_a_gpu_drop_packets_and_say_so(refgr, capfd):
     out = ours.run_demod(s)
     assert out.data().size == 0 and out.tags() == []
     assert "no usable CUDA device" in capfd.readouterr().err
+
+
+# ------------------------------------------------------------------ signal / signal2
+def same_sig_streams(ours_out, ref_out):
+    """Packets at the same items with the same tags; samples and channel to 1e-4 of the packet's peak (the rotation
+    factors come from two different cosf/sinf, see tests/test_gpu_signal.py); pad items are not compared (the
+    reference leaves them unwritten)."""
+    to, tr = ours_out[0].tags(), ref_out[0].tags()
+    assert [o for o, _ in to] == [o for o, _ in tr]
+    for a in range(1, len(ref_out)):
+        assert ours_out[a].tags() == [] and ref_out[a].tags() == []
+    do, dr = [s.data() for s in ours_out], [s.data() for s in ref_out]
+    for a in range(len(dr)):
+        assert do[a].shape == dr[a].shape
+    for (off, x), (_, y) in zip(to, tr):
+        assert set(x) == set(y)
+        for k in ("seq", "mcs", "len", "nsamp"):
+            assert x[k] == y[k], (k, x[k], y[k])
+        for k in ("cfo", "snr", "rssi"):
+            assert np.float32(x[k]) == np.float32(y[k]), (k, x[k], y[k])
+        assert np.all(np.abs(x["chan"] - y["chan"]) <= 1e-4 * np.abs(y["chan"]).max())
+        n = y["nsamp"]
+        for a in range(len(dr)):
+            ref = dr[a][off:off + n]
+            assert np.all(np.abs(do[a][off:off + n] - ref) <= 1e-4 * np.abs(ref).max()), "packet at %d antenna %d" % (off, a)
+    return len(tr)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nant", [1, 2])
+@pytest.mark.parametrize("chunks", [(0, 8192), (1000, 700), (4099, 8192)])
+def test_signal_block_stream_matches_the_reference(refgr, ours, nant, chunks):
+    if nant == 1:
+        bs = [gp.gen_batch(g.F_L, 5, 1, 300, 2, snr_db=30, seed=900), gp.gen_batch(g.F_HT, 6, 1, 800, 2, snr_db=30, seed=901),
+              gp.gen_batch(g.F_VHT, 7, 1, 1000, 2, snr_db=30, seed=902)]
+    else:
+        bs = [gp.gen_batch(g.F_HT, 11, 2, 600, 2, snr_db=35, seed=903), gp.gen_batch(g.F_VHT, 4, 2, 900, 2, snr_db=35, seed=904)]
+    raw, pos, rad = build_stream(bs, [0.0071, -0.0123, 0.0004], gap=500, noise=0.02)
+    # a false flag on noise before every packet and one inside every packet
+    allpos = np.sort(np.concatenate([pos, pos - 400, pos + 1000]))
+    rads = np.repeat(rad, 3)
+    ref_out = refgr.run_signal(raw, [int(x) for x in allpos], rad=rads, snr=21.5, rssi=-40.0)
+    our_out = ours.run_signal(raw, [int(x) for x in allpos], rad=rads, snr=21.5, rssi=-40.0, chunk_in=chunks[0], chunk_out=chunks[1])
+    assert same_sig_streams(our_out, ref_out) == len(pos)
+    # the rest of the chain on each side's own stream: same published messages
+    ref_msgs = refgr.run_decode(refgr.run_demod(ref_out))
+    our_msgs = ours.run_decode(ours.run_demod(our_out))
+    assert our_msgs == ref_msgs and len(ref_msgs) >= len(pos) - 1

@@ -54,3 +54,30 @@ def compare_with_reference(refgr, rx, batches, exact_llr=True):
             assert abs(float(d["sssnr0"]) - float(r["sssnr0"])) <= 1e-3 * max(1.0, abs(float(r["sssnr0"])))
     assert res.messages() == ref_msgs, "published messages differ (%d vs %d)" % (len(res.messages()), len(ref_msgs))
     return res, ref_msgs
+
+
+def build_stream(batches, rads, gap=300, seed=0, noise=1e-3):
+    """Concatenate the raw PPDUs of gen_batch() dicts into one stream per antenna, every packet with its own carrier
+    offset (rad per sample), separated by `gap` samples of noise.  -> (raw list, flag positions, rad per flag)"""
+    rng = np.random.default_rng(seed)
+    nant = batches[0]["nrx"]
+    parts = [[] for _ in range(nant)]
+    pos, rr = [], []
+    off = 0
+    k = 0
+    for b in batches:
+        npkt, n = b["ppdu"][0].shape
+        for p in range(npkt):
+            rad = float(rads[k % len(rads)])
+            k += 1
+            lead = (rng.standard_normal((nant, gap)) + 1j * rng.standard_normal((nant, gap))) * noise
+            rot = np.exp(-1j * rad * np.arange(n))
+            for a in range(nant):
+                parts[a].append(lead[a].astype(np.complex64))
+                parts[a].append((b["ppdu"][a][p].astype(np.complex128) * rot).astype(np.complex64))
+            pos.append(off + gap + b["sync_idx"])
+            rr.append(rad)
+            off += gap + n
+    tail = np.zeros(400, np.complex64)
+    raw = [np.concatenate(x + [tail]) for x in parts]
+    return raw, np.array(pos, np.int64), np.array(rr, np.float32)
