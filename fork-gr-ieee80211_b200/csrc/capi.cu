@@ -66,6 +66,8 @@ struct Slot {
 
 /* buffers of the signal stage (w80211_signal_batch) */
 struct SigStage {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {};
     DevBuf iq[2], syncs, res, chan_all, acc, out_iq[2], out_chan;
     PinBuf h_res, h_acc;
 };
@@ -618,6 +620,9 @@ void w80211_destroy(w80211_ctx* ctx)
             if (b->p) cudaFree(b->p);
         if (g.h_res.p) cudaFreeHost(g.h_res.p);
         if (g.h_acc.p) cudaFreeHost(g.h_acc.p);
+        for (auto& e : g.ev)
+            if (e) cudaEventDestroy(e);
+        if (g.stream) cudaStreamDestroy(g.stream);
     }
     if (ctx->d_tab) cudaFree(ctx->d_tab);
     delete ctx;
@@ -697,12 +702,15 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
         (in->nsamples > 0 && (!in->iq[0] || (in->nant == 2 && !in->iq[1]))) || in->start > in->nsamples)
         return fail(ctx, W80211_E_ARG, "bad signal_batch arguments");
     if (in->nsync > 0 && (!out->pkts || !out->chan)) return fail(ctx, W80211_E_ARG, "signal_batch: pkts / chan missing");
-    Slot& s = ctx->slots[0];
-    if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy");
     CK(cudaSetDevice(ctx->device));
-    cudaStream_t st = s.stream;
     SigStage& g = ctx->sig;
+    if (!g.stream) {
+        CK(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+        for (auto& e : g.ev) CK(cudaEventCreate(&e));
+    }
+    cudaStream_t st = g.stream;
     const int ns = in->nsync, nant = in->nant;
+    out->lsig_ms = out->copy_ms = 0.f;
     out->npkt = out->nsync_used = out->n_rejected = 0;
     out->iq_used = 0;
     out->next = in->start;
@@ -730,8 +738,10 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
     RS(dev_reserve(ctx, g.chan_all, (size_t)ns * 64 * 8));
     RS(pin_reserve(ctx, g.h_res, (size_t)ns * sizeof(int4)));
     CK(cudaMemcpyAsync(g.syncs.p, in->syncs, (size_t)ns * sizeof(w80211_sync), cudaMemcpyHostToDevice, st));
+    CK(cudaEventRecord(g.ev[0], st));
     w_launch_lsig(st, ctx->d_tab, ns, (const w80211_sync*)g.syncs.p, raw[0], in->nsamples, (int4*)g.res.p, (float2*)g.chan_all.p);
     CK(cudaGetLastError());
+    CK(cudaEventRecord(g.ev[1], st));
     CK(cudaMemcpyAsync(g.h_res.p, g.res.p, (size_t)ns * sizeof(int4), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     /* the block's state machine over the flags, in stream order (signal_impl.cc:76-160,194-201) */
@@ -797,6 +807,7 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
         out->nsync_used = ns;
         out->next = in->nsamples;
     }
+    CK(cudaEventElapsedTime(&out->lsig_ms, g.ev[0], g.ev[1]));
     if (np == 0) return W80211_OK;
     /* copy the accepted packets with their rotation */
     for (int a = 0; a < nant; a++)
@@ -817,14 +828,17 @@ int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_sign
     }
     RS(dev_reserve(ctx, g.acc, (size_t)np * sizeof(w_sig_acc)));
     CK(cudaMemcpyAsync(g.acc.p, acc, (size_t)np * sizeof(w_sig_acc), cudaMemcpyHostToDevice, st));
+    CK(cudaEventRecord(g.ev[2], st));
     w_launch_cfo_copy(st, np, nant, max_nsamp, (const w_sig_acc*)g.acc.p, raw[0], raw[1], dst[0], dst[1],
                       (const float2*)g.chan_all.p, dchan);
     CK(cudaGetLastError());
+    CK(cudaEventRecord(g.ev[3], st));
     if (out->mem != W80211_MEM_DEVICE) {
         for (int a = 0; a < nant; a++) CK(cudaMemcpyAsync(out->iq[a], dst[a], (size_t)used * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(out->chan, dchan, (size_t)np * 64 * 8, cudaMemcpyDeviceToHost, st));
     }
     CK(cudaStreamSynchronize(st));
+    CK(cudaEventElapsedTime(&out->copy_ms, g.ev[2], g.ev[3]));
     ctx->stats.kernel_launches += 2;
     return W80211_OK;
 }

@@ -72,7 +72,8 @@ class SignalIn(C.Structure):
 class SignalOut(C.Structure):
     _fields_ = [("mem", C.c_int32), ("npkt", C.c_int32), ("nsync_used", C.c_int32), ("n_rejected", C.c_int32),
                 ("next", C.c_uint64), ("need", C.c_uint64), ("iq_capacity", C.c_uint64), ("iq_used", C.c_uint64), ("pkts", C.c_void_p),
-                ("sync_of_pkt", C.c_void_p), ("chan", C.c_void_p), ("iq", C.c_void_p * 2)]
+                ("sync_of_pkt", C.c_void_p), ("chan", C.c_void_p), ("iq", C.c_void_p * 2),
+                ("lsig_ms", C.c_float), ("copy_ms", C.c_float)]
 
 
 class Stats(C.Structure):

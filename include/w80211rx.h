@@ -193,6 +193,7 @@ typedef struct w80211_signal_out {
     int32_t* sync_of_pkt;    /* host [>= nsync] or NULL: index into syncs[] of each packet */
     float* chan;             /* [>= nsync][64][2]: tag "chan" (signal_impl.cc:143) */
     float* iq[2];            /* CFO-corrected samples after L-SIG, nsamp per packet, packets back to back (no pad items) */
+    float lsig_ms, copy_ms;  /* out: CUDA-event durations of the two kernels of this call */
 } w80211_signal_out;
 
 /* Timing of the last completed batch, measured with CUDA events on the ctx's own stream (ms). */
@@ -226,7 +227,8 @@ void w80211_host_free(void* p);
  * parallel (CFO rotation, 3 FFTs, procLHSigDemodDeint cloud80211phy.cc:609-627, 24-step Viterbi, signalCheckLegacy
  * :650-728); the host then walks the flags in order the way the block's TRIGGER/DEMOD/COPY states would (a flag
  * inside an accepted packet, or within 80 samples after a rejected one, is never looked at) and a second kernel
- * copies the accepted packets with the per-sample rotation of signal_impl.cc:172-176.  Synchronous, uses slot 0.
+ * copies the accepted packets with the per-sample rotation of signal_impl.cc:172-176.  Synchronous, on a stream
+ * of its own (it may run while rx slots are in flight).
  * The rotation uses cosf/sinf: results agree with a host libm to 1 ulp of the factor, not bit for bit. */
 int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_signal_out* out);
 
