@@ -12,6 +12,8 @@
  *     decode_impl.cc:60-520                           -> w80211_decode_batch()
  * and a batch receiver that keeps the LLRs on the device calls
  *     w80211_rx_submit() / w80211_rx_collect()        (demod + decode fused, double buffered).
+ * The upstream neighbour signal / signal2 (include/gnuradio/ieee80211/signal.h:35, signal2.h:35) is covered by
+ *     signal_impl.cc:62-212, signal2_impl.cc:62-222   -> w80211_signal_batch()
  *
  * Conventions: plain C structs, caller owns every host buffer, the library owns
  * device memory and streams; int return, 0 = ok, < 0 = error (w80211_last_error());
