@@ -26,6 +26,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+TRACE = bool(os.environ.get("W80211_BENCH_TRACE"))  # per-call host and per-slot event times on stderr (diagnostics)
 METRIC = "decoded_psdu_gbit_per_s"
 UNIT = "Gbit/s"
 WORKLOAD = "C4: VHT MCS8 256-QAM r3/4 1SS long-GI, APEP 4092 B (MPDU 4088 B), AWGN 30 dB, 20 MHz"
@@ -206,7 +207,7 @@ def main_gpu(args):
     nsm = torch.cuda.get_device_properties(local).multi_processor_count
     # two full waves of the Viterbi kernel: 12 one-warp blocks per SM, one packet per lane
     P = args.packets if args.packets > 0 else nsm * 12 * 32 * 2
-    PE = min(P, args.e2e_packets if args.e2e_packets > 0 else nsm * 12 * 32 // 2)  # host-fed leg: PCIe-bound, smaller batches
+    PE = min(P, args.e2e_packets if args.e2e_packets > 0 else nsm * 12 * 32)  # host-fed legs: one full Viterbi wave per batch
     # ---- synthetic batch: N_UNIQUE distinct packets (own seed per rank), tiled to P packets per step
     ub = gen_unique(N_UNIQUE, 4 + 17 * rank)
     iq_u, pk_u, ch_u = host.pack_batch([ub])
@@ -236,8 +237,14 @@ def main_gpu(args):
     pk16 = pk[:PE].copy()
     pk16["iq_scale"] = np.tile(pk16_u["iq_scale"], reps_e)[:PE]
     pk16_host = torch.from_numpy(pk16.view(np.uint8).copy()).pin_memory()
+    q8_u, pk8_u, _ = host.quantize_sc16(iq_u, pk_u, bits=8)
+    iq8_host = torch.from_numpy(np.tile(q8_u[0], (reps_e, 1))[:PE * nsamp].copy()).pin_memory()
+    pk8 = pk[:PE].copy()
+    pk8["iq_scale"] = np.tile(pk8_u["iq_scale"], reps_e)[:PE]
+    pk8_host = torch.from_numpy(pk8.view(np.uint8).copy()).pin_memory()
 
-    rx = host.Receiver(local, nslots=2)
+    E2E_DEPTH = args.e2e_depth
+    rx = host.Receiver(local, nslots=max(2, E2E_DEPTH))
     bytes_cap = P * (MPDU_LEN + 72) + 4096
     mp_cap = 2 * P + 64
 
@@ -273,8 +280,11 @@ def main_gpu(args):
     bi_host16 = host.Receiver.make_in([iq16_host.data_ptr()], pk16_host.data_ptr(), ch_host.data_ptr(), mem=host.MEM_DEVICE,
                                       nsamples=PE * nsamp, npkt=PE, iq_format=host.IQ_SC16)
     bi_host16.mem = host.MEM_HOST
+    bi_host8 = host.Receiver.make_in([iq8_host.data_ptr()], pk8_host.data_ptr(), ch_host.data_ptr(), mem=host.MEM_DEVICE,
+                                     nsamples=PE * nsamp, npkt=PE, iq_format=host.IQ_SC8)
+    bi_host8.mem = host.MEM_HOST
     bo_d = [dev_out() for _ in range(2)]
-    bo_h = [host_out() for _ in range(2)]
+    bo_h = [host_out() for _ in range(max(2, E2E_DEPTH))]
     L, h = rx.L, rx.h
 
     def barrier():
@@ -293,7 +303,13 @@ def main_gpu(args):
 
         def collect(ps):
             nonlocal tot_bits, tot_ok
+            tc0 = time.perf_counter()
             rx._check(L.w80211_rx_collect(h, ps))
+            if TRACE:
+                t = rx.timing(ps)
+                print("trace collect slot %d wait %.2f ms | h2d %.2f hdr %.2f demod %.2f vit %.2f tb %.2f post %.2f d2h %.2f total %.2f plan %.2f coll %.2f"
+                      % (ps, (time.perf_counter() - tc0) * 1e3, t.h2d, t.header, t.demod, t.viterbi, t.traceback, t.post, t.d2h, t.total,
+                         t.host_plan, t.host_collect), file=sys.stderr)
             tot_bits += bos[ps][0].psdu_bits_ok
             tot_ok += bos[ps][0].n_crc_ok
             if tally:
@@ -303,10 +319,13 @@ def main_gpu(args):
                     stage[k] += getattr(t, k)
 
         for i in range(nsteps):
-            s = i & 1
+            s = i % depth
             if len(pend) == depth:
                 collect(pend.pop(0))
+            ts0 = time.perf_counter()
             rx._check(L.w80211_rx_submit(h, s, C.byref(bi), C.byref(bos[s][0])))
+            if TRACE:
+                print("trace submit slot %d took %.2f ms" % (s, (time.perf_counter() - ts0) * 1e3), file=sys.stderr)
             pend.append(s)
         for ps in pend:
             collect(ps)
@@ -335,17 +354,18 @@ def main_gpu(args):
 
     # ---- end-to-end legs: pinned host buffers -> C ABI -> pinned host results, two slots in flight
     def e2e_leg(bi):
-        run_steps(2, bi, bo_h, False)
+        run_steps(E2E_DEPTH, bi, bo_h, False, depth=E2E_DEPTH)
         barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record()
-        nbits, _ = run_steps(args.steps, bi, bo_h, False)
+        nbits, _ = run_steps(args.steps, bi, bo_h, False, depth=E2E_DEPTH)
         barrier()
         f1.record()
         f1.synchronize()
         return nbits, f0.elapsed_time(f1)
 
     e2e32_bits, e2e32_ms = e2e_leg(bi_host)    # fc32 samples on the wire (8 B per sample)
+    e2e8_bits, e2e8_ms = e2e_leg(bi_host8)     # sc8 samples on the wire (2 B per sample): reported beside the headline
     e2e_bits, e2e_ms = e2e_leg(bi_host16)      # sc16 samples on the wire (4 B per sample): the headline host-fed figure
     clk = clocks.stop(t_from, t_to)
 
@@ -402,13 +422,14 @@ def main_gpu(args):
     d2h = int(bo_h[0][0].n_bytes) + int(bo_h[0][0].n_mpdu) * 16 + 64 + PE * host.DESC_DTYPE.itemsize
 
     # ---- max over ranks, totals over ranks
-    vals = torch.tensor([ms, e2e_ms, e2e32_ms], dtype=torch.float64, device=dev)
-    sums = torch.tensor([float(bits), float(npk_ok), float(e2e_bits), float(launches), float(e2e32_bits)], dtype=torch.float64, device=dev)
+    vals = torch.tensor([ms, e2e_ms, e2e32_ms, e2e8_ms], dtype=torch.float64, device=dev)
+    sums = torch.tensor([float(bits), float(npk_ok), float(e2e_bits), float(launches), float(e2e32_bits), float(e2e8_bits)],
+                        dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
         dist.all_reduce(sums, op=dist.ReduceOp.SUM)
-    ms, e2e_ms, e2e32_ms = vals.tolist()
-    bits, npk_ok, e2e_bits, launches, e2e32_bits = sums.tolist()
+    ms, e2e_ms, e2e32_ms, e2e8_ms = vals.tolist()
+    bits, npk_ok, e2e_bits, launches, e2e32_bits, e2e8_bits = sums.tolist()
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -453,9 +474,13 @@ def main_gpu(args):
         "e2e": {"value": e2e_bits / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / K, "packets_per_step_per_gpu": PE,
                 "iq_wire_format": "sc16 + one scale per packet (SURVEY.md 8(f) N2), expanded to fc32 on the GPU",
-                "note": "pinned host buffers through w80211_rx_submit/collect, 2 slots in flight; PCIe-bound, so smaller batches than the resident leg"},
+                "slots_in_flight": E2E_DEPTH,
+                "note": "pinned host buffers through w80211_rx_submit/collect; PCIe-bound, so smaller batches than the resident leg and one more slot in flight to keep the copy engine busy while the host plans"},
         "e2e_fc32": {"value": e2e32_bits / (e2e32_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d32, "d2h_bytes_per_step": d2h,
                      "ms_per_step": e2e32_ms / K, "iq_wire_format": "fc32, the reference flowgraph's sample type"},
+        "e2e_sc8": {"value": e2e8_bits / (e2e8_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": PE * nsamp * 2 + pk_host.numel() + ch_host.numel() * 4,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e8_ms / K,
+                    "iq_wire_format": "sc8 + one scale per packet (UHD otw_format=sc8): 8-bit quantisation of the 30 dB samples, only FCS-valid bits are counted"},
         "gpu_launches": int(launches),
         "clocks": clk,
         "stage_ms_per_step": {k: v / KSEQ for k, v in stage.items()},
@@ -502,7 +527,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--packets", type=int, default=int(os.environ.get("W80211_BENCH_PACKETS", "0")),
                     help="packets per step and GPU (0 = two full waves of the Viterbi kernel: SMs x 12 x 32 x 2)")
-    ap.add_argument("--e2e-packets", type=int, default=0, help="packets per step and GPU of the host-fed leg (0 = SMs x 12 x 32 / 2)")
+    ap.add_argument("--e2e-packets", type=int, default=0, help="packets per step and GPU of the host-fed legs (0 = SMs x 12 x 32)")
+    ap.add_argument("--e2e-depth", type=int, default=3, help="slots in flight of the host-fed leg (2..4)")
     ap.add_argument("--mpdu-len", type=int, default=4088, help="profiling only: shorter packets; the reported workload is the default")
     ap.add_argument("--ref-packets", type=int, default=512, help="packets per core and step for the CPU reference")
     ap.add_argument("--no-cpu", action="store_true")

@@ -349,9 +349,10 @@ int finish_outputs(w80211_ctx* ctx, Slot& s)
 int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_batch_out* out, bool do_decode)
 {
     if (!in || !out || in->npkt < 0 || (in->nant != 1 && in->nant != 2) || !in->iq[0] || (in->nant == 2 && !in->iq[1]) ||
-        (in->npkt > 0 && (!in->pkts || !in->chan)) || (in->iq_format != W80211_IQ_FC32 && in->iq_format != W80211_IQ_SC16))
+        (in->npkt > 0 && (!in->pkts || !in->chan)) || (in->iq_format != W80211_IQ_FC32 && in->iq_format != W80211_IQ_SC16 && in->iq_format != W80211_IQ_SC8))
         return fail(ctx, W80211_E_ARG, "bad batch_in");
-    const bool sc16 = in->iq_format == W80211_IQ_SC16;
+    const bool sc16 = in->iq_format != W80211_IQ_FC32; /* integer wire format, expanded on the GPU */
+    const int raw_bytes = in->iq_format == W80211_IQ_SC8 ? 2 : 4;
     if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy: collect it first");
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = s.stream;
@@ -382,8 +383,8 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
         for (int a = 0; a < in->nant; a++) {
             RS(dev_reserve(ctx, s.iq[a], (size_t)in->nsamples * 8 + 1024));
             if (sc16) {
-                RS(dev_reserve(ctx, s.iq_raw[a], (size_t)in->nsamples * 4 + 1024));
-                CK(cudaMemcpyAsync(s.iq_raw[a].p, in->iq[a], (size_t)in->nsamples * 4, cudaMemcpyHostToDevice, st));
+                RS(dev_reserve(ctx, s.iq_raw[a], (size_t)in->nsamples * raw_bytes + 1024));
+                CK(cudaMemcpyAsync(s.iq_raw[a].p, in->iq[a], (size_t)in->nsamples * raw_bytes, cudaMemcpyHostToDevice, st));
             } else {
                 CK(cudaMemcpyAsync(s.iq[a].p, in->iq[a], (size_t)in->nsamples * 8, cudaMemcpyHostToDevice, st));
             }
@@ -391,7 +392,7 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
         }
         if (sc16) {
             w_launch_sc16_to_fc32(st, npkt, in->nant, d_pk, s.iq_raw[0].p, s.iq_raw[1].p, (float2*)s.iq[0].p, (float2*)s.iq[1].p,
-                                  in->nsamples);
+                                  in->nsamples, raw_bytes);
             CK(cudaGetLastError());
             if (npkt) s.launches += 1;
         }
@@ -407,7 +408,8 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
             }
         }
         if (sc16) {
-            w_launch_sc16_to_fc32(st, npkt, in->nant, d_pk, in->iq[0], in->iq[1], (float2*)s.iq[0].p, (float2*)s.iq[1].p, in->nsamples);
+            w_launch_sc16_to_fc32(st, npkt, in->nant, d_pk, in->iq[0], in->iq[1], (float2*)s.iq[0].p, (float2*)s.iq[1].p, in->nsamples,
+                                  raw_bytes);
             CK(cudaGetLastError());
             if (npkt) s.launches += 1;
         }

@@ -8,10 +8,11 @@
  * One block per packet; 4 bytes read and 8 written per sample, coalesced. */
 #include "common.cuh"
 
-__global__ void __launch_bounds__(256) sc16_to_fc32_kernel(int npkt, int nant, const w80211_pkt_in* __restrict__ pkts,
-                                                           const short2* __restrict__ raw0, const short2* __restrict__ raw1,
-                                                           float2* __restrict__ out0, float2* __restrict__ out1,
-                                                           unsigned long long nsamples)
+template <class RAW>
+__global__ void __launch_bounds__(256) int_to_fc32_kernel(int npkt, int nant, const w80211_pkt_in* __restrict__ pkts,
+                                                          const RAW* __restrict__ raw0, const RAW* __restrict__ raw1,
+                                                          float2* __restrict__ out0, float2* __restrict__ out1,
+                                                          unsigned long long nsamples)
 {
     const int p = blockIdx.x;
     if (p >= npkt) return;
@@ -19,20 +20,24 @@ __global__ void __launch_bounds__(256) sc16_to_fc32_kernel(int npkt, int nant, c
     if (pk.nsamp <= 0 || pk.iq_offset + (unsigned long long)pk.nsamp > nsamples) return; /* the header stage flags it */
     const float sc = pk.iq_scale;
     for (int a = 0; a < nant; a++) {
-        const short2* src = (a ? raw1 : raw0) + pk.iq_offset;
+        const RAW* src = (a ? raw1 : raw0) + pk.iq_offset;
         float2* dst = (a ? out1 : out0) + pk.iq_offset;
         for (int i = threadIdx.x; i < pk.nsamp; i += blockDim.x) {
-            const short2 v = __ldg(src + i);
+            const RAW v = __ldg(src + i);
             dst[i] = make_float2(__fmul_rn((float)v.x, sc), __fmul_rn((float)v.y, sc));
         }
     }
 }
 
+/* bytes_per_sample: 4 = sc16, 2 = sc8 */
 void w_launch_sc16_to_fc32(cudaStream_t st, int npkt, int nant, const w80211_pkt_in* pkts, const void* raw0, const void* raw1,
-                           float2* out0, float2* out1, unsigned long long nsamples)
+                           float2* out0, float2* out1, unsigned long long nsamples, int bytes_per_sample)
 {
     if (npkt <= 0) return;
-    sc16_to_fc32_kernel<<<npkt, 256, 0, st>>>(npkt, nant, pkts, (const short2*)raw0, (const short2*)raw1, out0, out1, nsamples);
+    if (bytes_per_sample == 2)
+        int_to_fc32_kernel<char2><<<npkt, 256, 0, st>>>(npkt, nant, pkts, (const char2*)raw0, (const char2*)raw1, out0, out1, nsamples);
+    else
+        int_to_fc32_kernel<short2><<<npkt, 256, 0, st>>>(npkt, nant, pkts, (const short2*)raw0, (const short2*)raw1, out0, out1, nsamples);
 }
 
 /* ------------------------------------------------------------------------------------------------

@@ -34,7 +34,7 @@ class PktIn(C.Structure):
 
 PKT_IN_DTYPE = np.dtype([("iq_offset", "<u8"), ("nsamp", "<i4"), ("l_mcs", "<i4"), ("l_len", "<i4"),
                          ("cfo", "<f4"), ("snr", "<f4"), ("rssi", "<f4"), ("iq_scale", "<f4")], align=True)
-IQ_FC32, IQ_SC16 = 0, 1
+IQ_FC32, IQ_SC16, IQ_SC8 = 0, 1, 2
 
 
 class BatchIn(C.Structure):
@@ -150,20 +150,22 @@ def pack_batch(batches):
     return [np.concatenate(x) for x in iq], np.concatenate(pk), np.concatenate(ch)
 
 
-def quantize_sc16(iq, pkts, headroom=0.9):
-    """fc32 packets -> the sc16 wire format: per packet, scale = max |component| / (32767 * headroom),
-    sample = round(x / scale).  Returns (int16 arrays [nsamples, 2], packet table with iq_scale set, the complex64
-    arrays a receiver of those int16 values reconstructs: (float)int16 * scale -- the reference's input for parity)."""
+def quantize_sc16(iq, pkts, headroom=0.9, bits=16):
+    """fc32 packets -> the sc16 (bits=16) or sc8 (bits=8) wire format: per packet,
+    scale = max |component| / (full_scale * headroom), sample = round(x / scale).  Returns (integer arrays [nsamples, 2],
+    packet table with iq_scale set, the complex64 arrays a receiver of those integers reconstructs:
+    (float)int * scale -- the reference's input for parity)."""
     pk = pkts.copy()
-    q = [np.zeros((len(x), 2), np.int16) for x in iq]
+    it, full = (np.int16, 32767.0) if bits == 16 else (np.int8, 127.0)
+    q = [np.zeros((len(x), 2), it) for x in iq]
     back = [np.zeros(len(x), np.complex64) for x in iq]
     for p in range(len(pk)):
         o, n = int(pk["iq_offset"][p]), int(pk["nsamp"][p])
         peak = max(float(np.abs(x[o:o + n].view(np.float32)).max()) if n else 0.0 for x in iq)
-        scale = np.float32(peak / (32767.0 * headroom)) if peak > 0 else np.float32(1.0)
+        scale = np.float32(peak / (full * headroom)) if peak > 0 else np.float32(1.0)
         pk["iq_scale"][p] = scale
         for a, x in enumerate(iq):
-            v = np.rint(x[o:o + n].view(np.float32).astype(np.float64) / float(scale)).astype(np.int16).reshape(-1, 2)
+            v = np.rint(x[o:o + n].view(np.float32).astype(np.float64) / float(scale)).astype(it).reshape(-1, 2)
             q[a][o:o + n] = v
             back[a][o:o + n] = (v.astype(np.float32) * scale).reshape(-1).view(np.complex64)
     return q, pk, back
@@ -233,10 +235,11 @@ class Receiver:
             bi.npkt = len(pkts)
             bi.nsamples = len(iq[0])
             if iq_format is None:
-                iq_format = IQ_SC16 if iq[0].dtype == np.int16 else IQ_FC32
+                iq_format = IQ_SC16 if iq[0].dtype == np.int16 else (IQ_SC8 if iq[0].dtype == np.int8 else IQ_FC32)
             for a, x in enumerate(iq):
                 assert x.flags.c_contiguous
-                assert (x.dtype == np.complex64) if iq_format == IQ_FC32 else (x.dtype == np.int16 and x.ndim == 2 and x.shape[1] == 2)
+                want = {IQ_FC32: np.complex64, IQ_SC16: np.int16, IQ_SC8: np.int8}[iq_format]
+                assert x.dtype == want and (iq_format == IQ_FC32 or (x.ndim == 2 and x.shape[1] == 2))
                 bi.iq[a] = x.ctypes.data
             assert pkts.dtype == PKT_IN_DTYPE
             bi.pkts = pkts.ctypes.data
