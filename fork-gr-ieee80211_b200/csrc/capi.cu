@@ -419,7 +419,7 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
     RS(dev_reserve(ctx, s.chan, (size_t)npkt * chan_stride * 8 + 16));
     RS(pin_reserve(ctx, s.h_desc, (size_t)npkt * sizeof(w80211_desc) + 16));
     w_launch_header(st, ctx->d_tab, npkt, in->nant, d_iq[0], d_iq[1], in->nsamples, d_pk, d_chin, (w80211_desc*)s.desc.p,
-                    (float2*)s.chan.p, chan_stride);
+                    (float2*)s.chan.p, chan_stride, in->mu_pos ? 1 : 0);
     CK(cudaGetLastError());
     if (npkt) s.launches += 1;
     CK(cudaEventRecord(s.ev[EV_HDR], st));

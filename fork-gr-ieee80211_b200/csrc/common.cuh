@@ -172,7 +172,7 @@ __host__ __device__ constexpr int w_branch_label(int st, int b)
 /* kernels (one translation unit each) */
 void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nant, const float2* iq0, const float2* iq1,
                      unsigned long long nsamples, const w80211_pkt_in* pk, const float2* chan_in, w80211_desc* desc,
-                     float2* chan_out, int chan_stride);
+                     float2* chan_out, int chan_stride, int mu_pos);
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nsymtot, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* sym_prefix,
                     const float2* chan, int chan_stride, float* llr);

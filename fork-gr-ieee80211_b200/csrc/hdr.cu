@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
                                                  const float2* __restrict__ iq0, const float2* __restrict__ iq1,
                                                  unsigned long long nsamples, const w80211_pkt_in* __restrict__ pkin,
                                                  const float2* __restrict__ chan_in, w80211_desc* __restrict__ desc_out,
-                                                 float2* __restrict__ chan_out, int chan_stride)
+                                                 float2* __restrict__ chan_out, int chan_stride, int mu_pos)
 {
     __shared__ HdrSmem S;
     const int p = blockIdx.x;
@@ -243,6 +243,8 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
 
     const uint8_t* b = S.bits;
     int sgi;
+    bool mu = false;       /* VHT MU PPDU on the one-antenna block (demod_impl.cc:347-379) */
+    bool sounding = false; /* two-stream VHT packet on the one-antenna block: only an NDP is meaningful (demod_impl.cc:393-409) */
     d.format = fmt;
     if (fmt == W80211_F_HT) {
         /* signalParserHt */
@@ -261,7 +263,16 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
         sgi = b[24];
         d.ampdu = 1;
         if (gid != 0 && gid != 63) {
-            d.status = W80211_ST_UNSUPPORTED; /* MU-MIMO: SURVEY.md 8(f) N4 */
+            /* MU: one stream for this user, two VHT-LTFs; modulation and length come from VHT-SIG-B
+             * (signalParserVhtA cloud80211phy.cc:1166-1173).  demod2 has no MU branch. */
+            if (nant == 2) {
+                d.status = W80211_ST_UNSUPPORTED;
+            } else {
+                mu = true;
+                d.nss = 1;
+                set_mod_nl(d, 0);
+                d.nltf = 2;
+            }
         } else {
             d.nss = bits_le(b, 10, 3) + 1;
             d.mcs = bits_le(b, 28, 4);
@@ -275,7 +286,12 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
     }
     d.nsymsamp = sgi ? 72 : 80;
     if (fmt == W80211_F_HT && d.nss > 2) d.status = W80211_ST_DROP_GATE;
-    if (d.status == W80211_ST_OK && nant == 1 && d.nss == 2) d.status = W80211_ST_UNSUPPORTED;
+    if (d.status == W80211_ST_OK && nant == 1 && d.nss == 2) {
+        if (fmt == W80211_F_VHT)
+            sounding = true;
+        else
+            d.status = W80211_ST_UNSUPPORTED;
+    }
     const int hdr_len = 160 + 80 + 80 * d.nltf + (fmt == W80211_F_VHT ? 80 : 0);
     if (d.status == W80211_ST_OK && pk.nsamp < hdr_len) d.status = W80211_ST_DROP_GATE;
     if (d.status != W80211_ST_OK) {
@@ -285,26 +301,45 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
 
     /* ---------------- non-legacy channel estimate ---------------- */
     const int sigb_at = 240 + 80 * d.nltf + 8;
-    if (d.nss == 1) {
-        /* H = FFT(LTF) / L_k on antenna 0 (demod_impl.cc:380-392, demod2_impl.cc:356-371) */
+    if (d.nss == 1 || sounding) {
+        if (fmt == W80211_F_VHT) {
+            /* group 0: VHT-SIG-B; group 1: the second VHT-LTF (MU only) */
+            float wr[8], wi[8], re[8], im[8];
+            fft64_twiddles(g, wr, wi);
+            fft64_lane8(grp == 0 ? x0 + sigb_at : x0 + 328, g, S.xch[grp], re, im, wr, wi, grp == 0 || (grp == 1 && mu));
+            if (grp < 2) {
+#pragma unroll
+                for (int k2 = 0; k2 < 8; k2++) S.F[grp][g + 8 * k2] = make_float2(re[k2], im[k2]);
+            }
+            __syncwarp();
+        }
+        /* H = FFT(LTF) / L_k on antenna 0 (demod_impl.cc:380-392, demod2_impl.cc:356-371); MU: from both LTFs with
+         * this user's row of the P matrix, pilots of the second LTF sign-flipped (LTF_NL_28_F_FLOAT_VHT22) */
 #pragma unroll
         for (int h = 0; h < 2; h++) {
             int i = lane + 32 * h;
             float l = T->ltf_nl[i];
             float2 v = make_float2(0.f, 0.f);
-            if (l != 0.0f) v = make_float2(__fdiv_rn(S.F[2][i].x, l), __fdiv_rn(S.F[2][i].y, l));
+            if (l != 0.0f) {
+                if (!mu) {
+                    v = make_float2(__fdiv_rn(S.F[2][i].x, l), __fdiv_rn(S.F[2][i].y, l));
+                } else {
+                    const cf32 f1 = c_make(S.F[2][i].x, S.F[2][i].y), f2 = c_make(S.F[1][i].x, S.F[1][i].y);
+                    cf32 hv;
+                    if (mu_pos == 0) {
+                        hv = c_divf(c_sub(f1, f2), __fmul_rn(l, 2.0f));
+                    } else {
+                        const float l22 = (i == 7 || i == 21 || i == 43 || i == 57) ? -l : l;
+                        hv = c_divf(c_add(c_divf(f1, l), c_divf(f2, l22)), 2.0f);
+                    }
+                    v = make_float2(hv.x, hv.y);
+                }
+            }
             cho[i] = v;
             S.eq[1][i] = v; /* keep H for SIG-B */
         }
         __syncwarp();
         if (fmt == W80211_F_VHT) {
-            float wr[8], wi[8], re[8], im[8];
-            fft64_twiddles(g, wr, wi);
-            fft64_lane8(x0 + sigb_at, g, S.xch[grp], re, im, wr, wi, grp == 0);
-            if (grp == 0) {
-#pragma unroll
-                for (int k2 = 0; k2 < 8; k2++) S.F[0][g + 8 * k2] = make_float2(re[k2], im[k2]);
-            }
             __syncwarp();
 #pragma unroll
             for (int h = 0; h < 2; h++) {
@@ -489,7 +524,7 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
             S.coded[T->sigb_int[2 * lane + 1]] = lab & 1;
         }
         __syncwarp();
-        if (lane < d.nss) {
+        if (lane < (nant == 1 ? 1 : d.nss)) {
             double np = 0.0;
             for (int i = 0; i < 52; i++) {
                 float qr = __fsub_rn(S.qam[lane][i].x, S.coded[i] ? 1.0f : -1.0f);
@@ -501,9 +536,20 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
         }
         __syncwarp();
         d.sssnr0 = S.llr[1][0];
-        d.sssnr1 = d.nss == 2 ? S.llr[1][1] : 0.0f;
-        /* signalParserVhtB, SU */
-        if (b[17] + b[18] + b[19] == 3) {
+        d.sssnr1 = (nant == 2 && d.nss == 2) ? S.llr[1][1] : 0.0f;
+        /* signalParserVhtB (cloud80211phy.cc:1180-1223): MU carries a 16-bit length and the user's MCS */
+        if (mu) {
+            d.len = bits_le(b, 0, 16) * 4;
+            d.mcs = bits_le(b, 16, 4);
+            if (d.mcs > 9) {
+                d.status = W80211_ST_UNSUPPORTED;
+                if (lane == 0) desc_out[p] = d;
+                return;
+            }
+            set_mod_nl(d, d.mcs);
+            d.nltf = 2;
+            d.nsym = (d.len * 8 + 22 + d.ndbps - 1) / d.ndbps;
+        } else if (b[17] + b[18] + b[19] == 3) {
             d.len = bits_le(b, 0, 17) * 4;
             d.nsym = (d.len * 8 + 22 + d.ndbps - 1) / d.ndbps;
         } else {
@@ -522,6 +568,8 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
         d.status = W80211_ST_DROP_GATE;
     } else if (d.nsym == 0) {
         d.status = W80211_ST_NDP;
+    } else if (sounding) {
+        d.status = W80211_ST_UNSUPPORTED; /* two streams of data on one antenna: the reference's output is undefined here */
     } else if (need > (long long)pk.nsamp) {
         d.status = W80211_ST_BAD_INPUT; /* nsamp tag shorter than the L-SIG duration it came from */
     }
@@ -532,10 +580,10 @@ __global__ void __launch_bounds__(32) hdr_kernel(const W80211Tables* __restrict_
 
 void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nant, const float2* iq0, const float2* iq1,
                      unsigned long long nsamples, const w80211_pkt_in* pk, const float2* chan_in, w80211_desc* desc,
-                     float2* chan_out, int chan_stride)
+                     float2* chan_out, int chan_stride, int mu_pos)
 {
     if (npkt <= 0) return;
-    hdr_kernel<<<npkt, 32, 0, st>>>(tab, npkt, nant, iq0, iq1, nsamples, pk, chan_in, desc, chan_out, chan_stride);
+    hdr_kernel<<<npkt, 32, 0, st>>>(tab, npkt, nant, iq0, iq1, nsamples, pk, chan_in, desc, chan_out, chan_stride, mu_pos);
 }
 
 /* ------------------------------------------------------------------------------------------------

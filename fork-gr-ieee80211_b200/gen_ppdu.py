@@ -25,9 +25,17 @@ def _nl_ltf(m, iss, n, shift):
     return g._ofdm(g._csd(f, shift), 16, 56 * m.nss)
 
 
-def _sigb_symbol(m, shift):
+NDP_SIGB_PATTERN = 0b01000010001011100000  # 20 MHz NDP VHT-SIG-B (21.3.8.3.6), bit 0 first; cloud80211phy.cc:1211
+
+
+def _sigb_symbol(m, shift, ndp=False, mu=False):
     nw = (m.len + 3) // 4
-    b = np.concatenate([g.int_to_bits(nw, 17), [1, 1, 1], np.zeros(6, np.uint8)]).astype(np.uint8)
+    if ndp:
+        b = np.concatenate([g.int_to_bits(NDP_SIGB_PATTERN, 20), np.zeros(6, np.uint8)]).astype(np.uint8)
+    elif mu:  # MU: 16-bit length in 4-byte units, 4-bit MCS, tail (Table 21-14)
+        b = np.concatenate([g.int_to_bits(nw, 16), g.int_to_bits(m.mcs, 4), np.zeros(6, np.uint8)]).astype(np.uint8)
+    else:
+        b = np.concatenate([g.int_to_bits(nw, 17), [1, 1, 1], np.zeros(6, np.uint8)]).astype(np.uint8)
     coded = g.bcc_encode(b[None, :])[0]
     inter = g._interleave(coded, g.interleave_perm(52, 1, False, 1))
     f = np.zeros(64, complex)
@@ -61,8 +69,24 @@ def vht_siga_bits(m, short_gi):
     return b
 
 
+def vht_siga_bits_mu(gid, short_gi):
+    """VHT-SIG-A of a two-user MU PPDU, one space-time stream per user, BCC for both (Table 21-12)."""
+    b = np.zeros(48, np.uint8)
+    b[2] = 1
+    b[4:10] = g.int_to_bits(gid, 6)
+    b[10:13] = g.int_to_bits(1, 3)  # user position 0: one stream
+    b[13:16] = g.int_to_bits(1, 3)  # user position 1: one stream
+    b[23] = 1
+    b[24] = 1 if short_gi else 0
+    b[31] = 1  # coding of user 3: reserved 1 when the position is empty
+    b[33] = 1
+    b[34:42] = g.crc8_sig(b[None, :34])[0]
+    return b
+
+
 def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, chan=None, nrx=None,
-              mpdus=None, corrupt_sig=False, corrupt_fcs=False, l_len_short=0, lead=0, trail=0):
+              mpdus=None, corrupt_sig=False, corrupt_fcs=False, l_len_short=0, lead=0, trail=0,
+              ndp=False, mu_pos=None, mu_gid=2):
     """Generate npkt packets of one configuration.
 
     length: PSDU bytes for legacy / HT; MPDU bytes for VHT (wrapped in a one-subframe A-MPDU, so the
@@ -72,6 +96,10 @@ def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, 
     corrupt_sig: flip one HT-SIG / VHT-SIG-A bit after the CRC was computed (dropped by the SIG check).
     corrupt_fcs: flip one payload bit (packet decodes, FCS fails).
     l_len_short: subtract this many OFDM symbols from the L-SIG duration (dropped by the length gate).
+    ndp:    VHT null data packet (sounding): no data field, the NDP pattern in VHT-SIG-B.
+    mu_pos: 0 or 1: a VHT MU PPDU (group id mu_gid) as the user at that position receives it once the other user's
+            stream is nulled: legacy part and VHT-SIG-A from chain 0, then VHT-STF, two VHT-LTFs with row mu_pos of the
+            P matrix, the MU VHT-SIG-B and one stream of data.  fmt must be VHT, nss 1.
     Returns a dict, see the bottom of this function."""
     rng = np.random.default_rng(seed)
     if mpdus is None:
@@ -83,11 +111,18 @@ def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, 
     m = g.Mod(fmt, mcs, nss, psdu.shape[1], short_gi)
     nrx = nrx or m.nss
     streams, bits = g.data_field_bits(m, psdu)
+    mu = mu_pos is not None
+    if mu:
+        assert fmt == g.F_VHT and nss == 1 and not ndp
+        m.nltf = 2
+    if ndp:
+        assert fmt == g.F_VHT
 
     tx = []
     for iss in range(m.nss):
         sh_l = 4 * iss  # legacy-portion cyclic shift, -200 ns on chain 2
-        sh_nl = 8 * iss  # HT/VHT-portion cyclic shift, -400 ns on stream 2
+        sh_nl = 8 * (mu_pos if mu else iss)  # HT/VHT-portion cyclic shift, -400 ns on stream 2
+        row = mu_pos if mu else iss  # row of the P matrix this stream's LTFs carry
         parts = [np.broadcast_to(_legacy_preamble(sh_l), (npkt, 320))]
         post_len = 0
         if fmt == g.F_L:
@@ -95,14 +130,14 @@ def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, 
             data = g._data_symbols(m, streams[iss], iss, sh_l)
         else:
             l_mcs = 0
-            nlsym_data = -(-(m.nsym * m.nsym_samp) // 80)
+            nlsym_data = 0 if ndp else -(-(m.nsym * m.nsym_samp) // 80)
             nlsym = 2 + 1 + m.nltf + (1 if fmt == g.F_VHT else 0) + nlsym_data - l_len_short
             l_len = nlsym * 3 - 3
             data = g._data_symbols(m, streams[iss], iss, sh_nl)
         lsig = g._interleave(g.bcc_encode(g._lsig_bits(l_mcs, l_len)[None, :])[0], g.interleave_perm(48, 1, True))
         parts.append(np.broadcast_to(g._sig_symbol(lsig, False, g.PILOT_POLARITY[0], sh_l), (npkt, 80)))
         if fmt != g.F_L:
-            sb = ht_sig_bits(m, short_gi) if fmt == g.F_HT else vht_siga_bits(m, short_gi)
+            sb = ht_sig_bits(m, short_gi) if fmt == g.F_HT else (vht_siga_bits_mu(mu_gid, short_gi) if mu else vht_siga_bits(m, short_gi))
             if corrupt_sig:
                 sb = sb.copy()
                 sb[9] ^= 1
@@ -111,11 +146,12 @@ def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, 
             s1 = g._sig_symbol(g._interleave(c[:48], perm), fmt == g.F_HT, g.PILOT_POLARITY[1], sh_l)
             s2 = g._sig_symbol(g._interleave(c[48:], perm), True, g.PILOT_POLARITY[2], sh_l)
             stf = g._ofdm(g._csd(g._to_fft_bins(g._STF, 26), sh_nl), 16, 12 * m.nss)
-            nl = [s1, s2, stf] + [_nl_ltf(m, iss, n, sh_nl) for n in range(m.nltf)]
+            nl = [s1, s2, stf] + [_nl_ltf(m, row, n, sh_nl) for n in range(m.nltf)]
             if fmt == g.F_VHT:
-                nl.append(_sigb_symbol(m, sh_nl)[0])
+                nl.append(_sigb_symbol(m, sh_nl, ndp=ndp, mu=mu)[0])
             parts.append(np.broadcast_to(np.concatenate(nl), (npkt, sum(len(x) for x in nl))))
-        parts.append(data)
+        if not ndp:
+            parts.append(data)
         tx.append(np.concatenate(parts, axis=1))
     tx = np.stack(tx, axis=0)  # [nss, P, n]
 

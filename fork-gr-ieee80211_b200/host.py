@@ -39,7 +39,8 @@ IQ_FC32, IQ_SC16, IQ_SC8 = 0, 1, 2
 
 class BatchIn(C.Structure):
     _fields_ = [("npkt", C.c_int32), ("nant", C.c_int32), ("mem", C.c_int32), ("iq_format", C.c_int32),
-                ("iq", C.c_void_p * 2), ("nsamples", C.c_uint64), ("pkts", C.c_void_p), ("chan", C.c_void_p)]
+                ("iq", C.c_void_p * 2), ("nsamples", C.c_uint64), ("pkts", C.c_void_p), ("chan", C.c_void_p),
+                ("mu_pos", C.c_int32), ("reserved", C.c_int32)]
 
 
 DESC_DTYPE = np.dtype([
@@ -226,7 +227,7 @@ class Receiver:
 
     # -- raw struct helpers -------------------------------------------------
     @staticmethod
-    def make_in(iq, pkts, chan, mem=MEM_HOST, nsamples=None, npkt=None, iq_format=None):
+    def make_in(iq, pkts, chan, mem=MEM_HOST, nsamples=None, npkt=None, iq_format=None, mu_pos=0):
         """iq: list of numpy arrays (host: complex64, or int16 of shape [nsamples, 2] for sc16) or integer device pointers."""
         bi = BatchIn()
         bi.nant = len(iq)
@@ -253,6 +254,7 @@ class Receiver:
             bi.pkts = int(pkts)
             bi.chan = int(chan)
         bi.iq_format = int(iq_format or 0)
+        bi.mu_pos = int(mu_pos)
         return bi
 
     @staticmethod
@@ -285,18 +287,18 @@ class Receiver:
         return nsamp_tot * 2 + 64 * len(pkts) + 64, len(pkts) * 2 + nsamp_tot // 64 + 64, \
             nsamp_tot * 12 + 64 * len(pkts) + 64
 
-    def rx(self, iq, pkts, chan, want_llr=False):
+    def rx(self, iq, pkts, chan, want_llr=False, mu_pos=0):
         """IQ -> bytes, fused (w80211_rx_batch)."""
         bcap, mcap, lcap = self._caps(iq, pkts)
-        bi = self.make_in(iq, pkts, chan)
+        bi = self.make_in(iq, pkts, chan, mu_pos=mu_pos)
         bo, arrs = self.make_out_host(len(pkts), bcap, mcap, lcap if want_llr else 0)
         self._check(self.L.w80211_rx_batch(self.h, C.byref(bi), C.byref(bo)))
         return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo, arrs["llr"])
 
-    def demod(self, iq, pkts, chan):
+    def demod(self, iq, pkts, chan, mu_pos=0):
         """IQ -> LLR stream + descriptors (w80211_demod_batch): what demod / demod2 output."""
         bcap, mcap, lcap = self._caps(iq, pkts)
-        bi = self.make_in(iq, pkts, chan)
+        bi = self.make_in(iq, pkts, chan, mu_pos=mu_pos)
         bo, arrs = self.make_out_host(len(pkts), 16, 1, lcap)
         self._check(self.L.w80211_demod_batch(self.h, C.byref(bi), C.byref(bo)))
         return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo, arrs["llr"])

@@ -37,7 +37,10 @@ decode_impl::decode_impl(bool ifdebug)
     cfg.device = d_env.device;
     cfg.max_packets = d_env.max_batch;
     cfg.nslots = 1;
-    int r = w80211_create(&cfg, &d_ctx);
+    int r = w80211_abi_version() == W80211_ABI_VERSION ? w80211_create(&cfg, &d_ctx) : W80211_E_ARG;
+    if (w80211_abi_version() != W80211_ABI_VERSION)
+        std::fprintf(stderr, "ieee80211 %s: libw80211rx.so has ABI version %d, this block was built for %d\n", "decode",
+                     w80211_abi_version(), W80211_ABI_VERSION);
     if (r != W80211_OK) {
         d_ctx = nullptr;
         d_failed = true;

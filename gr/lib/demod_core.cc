@@ -70,9 +70,10 @@ rx_env rx_env::read()
 }
 
 /* ------------------------------------------------------------------ demod_core */
-demod_core::demod_core(gr::block* owner, int nant, const char* label)
+demod_core::demod_core(gr::block* owner, int nant, const char* label, int mupos)
     : d_blk(owner),
       d_nant(nant),
+      d_mupos(mupos ? 1 : 0),
       d_label(label),
       d_env(rx_env::read()),
       d_ctx(nullptr),
@@ -88,7 +89,10 @@ demod_core::demod_core(gr::block* owner, int nant, const char* label)
     cfg.device = d_env.device;
     cfg.max_packets = d_env.max_batch;
     cfg.nslots = 1;
-    int r = w80211_create(&cfg, &d_ctx);
+    int r = w80211_abi_version() == W80211_ABI_VERSION ? w80211_create(&cfg, &d_ctx) : W80211_E_ARG;
+    if (w80211_abi_version() != W80211_ABI_VERSION)
+        std::fprintf(stderr, "ieee80211 %s: libw80211rx.so has ABI version %d, this block was built for %d\n", d_label.c_str(),
+                     w80211_abi_version(), W80211_ABI_VERSION);
     if (r != W80211_OK) {
         d_ctx = nullptr;
         d_failed = true;
@@ -203,6 +207,7 @@ void demod_core::run_batch()
     d_desc.assign((size_t)npkt, w80211_desc());
     d_emit.clear();
     d_emit_pos = 0;
+    d_ndp_chan.clear();
     if (!d_failed && npkt > 0) {
         uint64_t nsamp_tot = 0;
         for (int p = 0; p < npkt; p++) nsamp_tot += (uint64_t)d_pkts[p].nsamp;
@@ -220,6 +225,7 @@ void demod_core::run_batch()
             in.nsamples = d_fill;
             in.pkts = d_pkts.data();
             in.chan = d_chan.data();
+            in.mu_pos = d_mupos;
             w80211_batch_out out;
             std::memset(&out, 0, sizeof(out));
             out.mem = W80211_MEM_HOST;
@@ -233,9 +239,20 @@ void demod_core::run_batch()
                 for (auto& d : d_desc) d.status = W80211_ST_BAD_INPUT;
             }
             for (int p = 0; p < npkt; p++) {
-                /* packets that fail the reference's gates go to its CLEAN state without output
-                 * (demod_impl.cc:159,186); NDPs and MU packets are outside this library */
-                if (d_desc[p].status == W80211_ST_OK && d_desc[p].total > 0) d_emit.push_back(emit_item{ p, 0 });
+                /* packets that fail the reference's gates go to its CLEAN state without output (demod_impl.cc:159,186) */
+                if (d_desc[p].status == W80211_ST_OK && d_desc[p].total > 0) {
+                    d_emit.push_back(emit_item{ p, 0, -1 });
+                } else if (d_desc[p].status == W80211_ST_NDP && d_nant == 1 && d_desc[p].nss == 2 && d_pkts[p].nsamp >= 392) {
+                    /* two-stream VHT NDP on the one-antenna block: the 2 x 64 raw samples of the two VHT-LTFs travel
+                     * to decode in the tag "mu2x1chan" with 1024 placeholder items (demod_impl.cc:238-271,396-398) */
+                    const std::complex<float>* x = reinterpret_cast<const std::complex<float>*>(d_iq[0].data()) + d_pkts[p].iq_offset;
+                    std::vector<std::complex<float>> h(128);
+                    std::copy(x + 248, x + 312, h.begin());
+                    std::copy(x + 328, x + 392, h.begin() + 64);
+                    d_ndp_chan.push_back(h);
+                    d_desc[p].total = 1024;
+                    d_emit.push_back(emit_item{ p, 0, (int)d_ndp_chan.size() - 1 });
+                }
             }
         }
     }
@@ -257,7 +274,7 @@ void demod_core::run_batch()
 }
 
 /* The tags of demod_impl.cc:224-253 / demod2_impl.cc:229-250 on the packet's first LLR. */
-void demod_core::write_tags(const w80211_desc& d, uint64_t abs_offset)
+void demod_core::write_tags(const w80211_desc& d, uint64_t abs_offset, int ndp)
 {
     const pmt::pmt_t src = d_blk->alias_pmt();
     auto put_f = [&](const char* k, float v) { d_blk->add_item_tag(0, abs_offset, pmt::mp(k), pmt::from_float(v), src); };
@@ -275,6 +292,10 @@ void demod_core::write_tags(const w80211_desc& d, uint64_t abs_offset)
     put_l("cr", d.cr);
     put_l("ampdu", d.ampdu);
     put_l("trellis", d.trellis);
+    if (ndp >= 0) {
+        const auto& h = d_ndp_chan[(size_t)ndp];
+        d_blk->add_item_tag(0, abs_offset, pmt::mp("mu2x1chan"), pmt::init_c32vector(h.size(), h), src);
+    }
     put_l("total", d.total);
 }
 
@@ -285,9 +306,12 @@ int demod_core::emit(float* out, int room, int already)
     while (d_emit_pos < d_emit.size() && produced < room) {
         emit_item& e = d_emit[d_emit_pos];
         const w80211_desc& d = d_desc[(size_t)e.pkt];
-        if (e.written == 0) write_tags(d, d_blk->nitems_written(0) + (uint64_t)(already + produced));
+        if (e.written == 0) write_tags(d, d_blk->nitems_written(0) + (uint64_t)(already + produced), e.ndp);
         const size_t n = std::min<size_t>((size_t)(room - produced), (size_t)d.total - e.written);
-        std::memcpy(out + produced, d_llr.data() + d.llr_off + e.written, n * sizeof(float));
+        if (e.ndp >= 0)
+            std::memset(out + produced, 0, n * sizeof(float)); /* the reference leaves these items unwritten */
+        else
+            std::memcpy(out + produced, d_llr.data() + d.llr_off + e.written, n * sizeof(float));
         e.written += n;
         produced += (int)n;
         if (e.written == (size_t)d.total) d_emit_pos++;

@@ -20,6 +20,7 @@
 #define INCLUDED_IEEE80211_DEMOD_CORE_H
 
 #include <chrono>
+#include <complex>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -63,7 +64,7 @@ struct rx_env {
 class demod_core
 {
 public:
-    demod_core(gr::block* owner, int nant, const char* label);
+    demod_core(gr::block* owner, int nant, const char* label, int mupos = 0);
     ~demod_core();
 
     void forecast(int noutput_items, gr_vector_int& ninput_items_required);
@@ -77,17 +78,19 @@ private:
     struct emit_item {
         int pkt;        /* index into d_desc */
         size_t written; /* floats of this packet already written to the output */
+        int ndp;        /* >= 0: a sounding packet, index into d_ndp_chan; its 1024 output items carry no LLRs */
     };
 
     int ingest(int navail, gr_vector_const_void_star& input_items);
     bool start_packet(uint64_t abs_offset);
     void run_batch();
     int emit(float* out, int room, int already);
-    void write_tags(const w80211_desc& d, uint64_t abs_offset);
+    void write_tags(const w80211_desc& d, uint64_t abs_offset, int ndp);
     void report(const char* what);
 
     gr::block* d_blk;
     const int d_nant;
+    const int d_mupos;
     const std::string d_label;
     rx_env d_env;
     w80211_ctx* d_ctx;
@@ -107,6 +110,7 @@ private:
     std::vector<w80211_desc> d_desc;
     std::vector<emit_item> d_emit;
     size_t d_emit_pos;
+    std::vector<std::vector<std::complex<float>>> d_ndp_chan; /* tag "mu2x1chan" of the batch's sounding packets */
 };
 
 } // namespace ieee80211

@@ -13,7 +13,7 @@ demod_impl::demod_impl(int mupos, int mugid)
     : gr::block("demod", gr::io_signature::make(1, 1, sizeof(gr_complex)), gr::io_signature::make(1, 1, sizeof(float))),
       d_mupos(mupos),
       d_mugid(mugid),
-      d_core(this, 1, "demod")
+      d_core(this, 1, "demod", mupos)
 {
     set_tag_propagation_policy(block::TPP_DONT);
 }

@@ -21,7 +21,7 @@ public:
                      gr_vector_void_star& output_items) override;
 
 private:
-    int d_mupos, d_mugid; /* kept for the factory signature; the MU-MIMO path is not part of this library */
+    int d_mupos, d_mugid; /* mupos selects the MU channel estimate; the reference never reads mugid either (demod_impl.cc:38-39) */
     demod_core d_core;
 };
 

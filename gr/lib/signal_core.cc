@@ -31,7 +31,10 @@ signal_core::signal_core(gr::block* owner, int nant, const char* label)
     cfg.device = d_env.device;
     cfg.max_packets = d_env.max_batch;
     cfg.nslots = 1;
-    int r = w80211_create(&cfg, &d_ctx);
+    int r = w80211_abi_version() == W80211_ABI_VERSION ? w80211_create(&cfg, &d_ctx) : W80211_E_ARG;
+    if (w80211_abi_version() != W80211_ABI_VERSION)
+        std::fprintf(stderr, "ieee80211 %s: libw80211rx.so has ABI version %d, this block was built for %d\n", d_label.c_str(),
+                     w80211_abi_version(), W80211_ABI_VERSION);
     if (r != W80211_OK) {
         d_ctx = nullptr;
         d_failed = true;

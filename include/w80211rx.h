@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define W80211_ABI_VERSION 3
+#define W80211_ABI_VERSION 4
 
 /* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
 #define W80211_F_L 0
@@ -104,6 +104,9 @@ typedef struct w80211_batch_in {
     uint64_t nsamples;       /* length of each iq[] array in complex samples */
     const w80211_pkt_in* pkts; /* [npkt] */
     const float* chan;       /* [npkt][64][2]: tag "chan", legacy channel in natural FFT order (signal_impl.cc:143) */
+    int32_t mu_pos;          /* nant = 1 only: this receiver's user position (0 or 1) in a VHT MU PPDU, the `mupos` argument of
+                                demod::make (demod_impl.cc:34-39, 347-379); SU packets ignore it */
+    int32_t reserved;
 } w80211_batch_in;
 
 /* Per-packet parameters: the reference's c8p_mod (lib/cloud80211phy.h:58-98) plus the
