@@ -70,6 +70,9 @@ struct SigStage {
     cudaEvent_t ev[4] = {};
     DevBuf iq[2], syncs, res, chan_all, acc, out_iq[2], out_chan;
     PinBuf h_res, h_acc;
+    /* detection stage */
+    DevBuf det_ac, det_conj, det_sig, det_cnt, det_starts, det_ends, det_ev, det_res;
+    PinBuf h_edges, h_ev, h_dres;
 };
 
 } // namespace
@@ -558,6 +561,9 @@ size_t w80211_sizeof(int what)
     case 8: return sizeof(w80211_sync);
     case 9: return sizeof(w80211_signal_in);
     case 10: return sizeof(w80211_signal_out);
+    case 11: return sizeof(w80211_detect_state);
+    case 12: return sizeof(w80211_detect_in);
+    case 13: return sizeof(w80211_detect_out);
     default: return 0;
     }
 }
@@ -617,11 +623,15 @@ void w80211_destroy(w80211_ctx* ctx)
     }
     {
         SigStage& g = ctx->sig;
-        DevBuf* db[] = {&g.iq[0], &g.iq[1], &g.syncs, &g.res, &g.chan_all, &g.acc, &g.out_iq[0], &g.out_iq[1], &g.out_chan};
+        DevBuf* db[] = {&g.iq[0], &g.iq[1], &g.syncs, &g.res, &g.chan_all, &g.acc, &g.out_iq[0], &g.out_iq[1], &g.out_chan,
+                        &g.det_ac, &g.det_conj, &g.det_sig, &g.det_cnt, &g.det_starts, &g.det_ends, &g.det_ev, &g.det_res};
         for (DevBuf* b : db)
             if (b->p) cudaFree(b->p);
         if (g.h_res.p) cudaFreeHost(g.h_res.p);
         if (g.h_acc.p) cudaFreeHost(g.h_acc.p);
+        if (g.h_edges.p) cudaFreeHost(g.h_edges.p);
+        if (g.h_ev.p) cudaFreeHost(g.h_ev.p);
+        if (g.h_dres.p) cudaFreeHost(g.h_dres.p);
         for (auto& e : g.ev)
             if (e) cudaEventDestroy(e);
         if (g.stream) cudaStreamDestroy(g.stream);
@@ -695,6 +705,179 @@ int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out
     int r = w80211_rx_submit(ctx, 0, in, out);
     if (r < 0) return r;
     return w80211_rx_collect(ctx, 0);
+}
+
+int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_detect_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (!in || !out || in->nsamples >= 0xffffffffull || (in->nsamples > 0 && (!in->preac || !in->preconj || !in->sig)) ||
+        out->sync_capacity < 0 || (out->sync_capacity > 0 && !out->syncs))
+        return fail(ctx, W80211_E_ARG, "bad detect_batch arguments");
+    w80211_detect_state st0;
+    memset(&st0, 0, sizeof(st0));
+    if (in->state) st0 = *in->state;
+    if (st0.n_plateau < 0 || st0.count_down < 0 || st0.count_down > 80 || st0.sync_skip < 0)
+        return fail(ctx, W80211_E_ARG, "detect_batch: impossible carried state");
+    const long long n = (long long)in->nsamples;
+    out->nsync = out->n_trigger = 0;
+    out->next = in->nsamples;
+    out->state = st0;
+    if (n == 0) return W80211_OK;
+    CK(cudaSetDevice(ctx->device));
+    SigStage& g = ctx->sig;
+    if (!g.stream) {
+        CK(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+        for (auto& e : g.ev) CK(cudaEventCreate(&e));
+    }
+    cudaStream_t st = g.stream;
+    const float* d_ac = in->preac;
+    const float2* d_cj = (const float2*)in->preconj;
+    const float2* d_sg = (const float2*)in->sig;
+    if (in->mem != W80211_MEM_DEVICE) {
+        RS(dev_reserve(ctx, g.det_ac, (size_t)n * 4 + 64));
+        RS(dev_reserve(ctx, g.det_conj, (size_t)n * 8 + 64));
+        RS(dev_reserve(ctx, g.det_sig, (size_t)n * 8 + 64));
+        CK(cudaMemcpyAsync(g.det_ac.p, in->preac, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(g.det_conj.p, in->preconj, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(g.det_sig.p, in->sig, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+        d_ac = (const float*)g.det_ac.p;
+        d_cj = (const float2*)g.det_conj.p;
+        d_sg = (const float2*)g.det_sig.p;
+    }
+    /* ---- runs of preac > 0.3 */
+    const unsigned int cap = (unsigned int)(n / 2 + 2);
+    RS(dev_reserve(ctx, g.det_cnt, 16));
+    RS(dev_reserve(ctx, g.det_starts, (size_t)cap * 4));
+    RS(dev_reserve(ctx, g.det_ends, (size_t)cap * 4));
+    CK(cudaMemsetAsync(g.det_cnt.p, 0, 16, st));
+    w_launch_run_edges(st, d_ac, (unsigned long long)n, st0.n_plateau > 0, cap, (unsigned int*)g.det_cnt.p, (unsigned int*)g.det_starts.p,
+                       (unsigned int*)g.det_ends.p);
+    CK(cudaGetLastError());
+    RS(pin_reserve(ctx, g.h_edges, 16));
+    CK(cudaMemcpyAsync(g.h_edges.p, g.det_cnt.p, 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const unsigned int ns = ((unsigned int*)g.h_edges.p)[0], ne = ((unsigned int*)g.h_edges.p)[1];
+    if (ns > cap || ne > cap) return fail(ctx, W80211_E_STATE, "detect_batch: edge list overflow");
+    RS(pin_reserve(ctx, g.h_edges, (size_t)(ns + ne) * 4 + 16));
+    unsigned int* hs = (unsigned int*)g.h_edges.p;
+    unsigned int* he = hs + ns;
+    if (ns) CK(cudaMemcpyAsync(hs, g.det_starts.p, (size_t)ns * 4, cudaMemcpyDeviceToHost, st));
+    if (ne) CK(cudaMemcpyAsync(he, g.det_ends.p, (size_t)ne * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    std::sort(hs, hs + ns);
+    std::sort(he, he + ne);
+    struct Run {
+        long long s, e; /* [s, e): s < 0 when the run began before this buffer, e = n when it is still open */
+        long long i0;   /* sample at which this run started a countdown, -1: none */
+        bool fpe0;      /* carried d_fPlateauEnd */
+    };
+    std::vector<Run> runs;
+    runs.reserve((size_t)ns + 1);
+    const bool cont = st0.n_plateau > 0;
+    if (cont) runs.push_back(Run{ -(long long)st0.n_plateau, n, -1, st0.f_plateau_end != 0 });
+    for (unsigned int k = 0; k < ns; k++) runs.push_back(Run{ (long long)hs[k], n, -1, false });
+    if (ne > runs.size() || ne + 1 < runs.size()) return fail(ctx, W80211_E_STATE, "detect_batch: run edges do not pair up");
+    for (unsigned int k = 0; k < ne; k++) runs[k].e = (long long)he[k];
+    /* ---- the trigger block's plateau / countdown logic over the runs (trigger_impl.cc:76-108) */
+    std::vector<long long> trig; /* samples that carry the 0x01 flag, ascending; may lie beyond this buffer */
+    long long busy_until = -1;   /* d_fPlateau is set up to and including this sample */
+    if (st0.count_down > 0) {
+        busy_until = (long long)st0.count_down - 1;
+        trig.push_back(busy_until);
+    }
+    for (auto& r : runs) {
+        if (r.fpe0) continue; /* one countdown per run */
+        const long long i0 = std::max(std::max(r.s + 20, busy_until + 1), 0ll);
+        if (i0 < r.e) {
+            r.i0 = i0;
+            busy_until = i0 + 79;
+            trig.push_back(busy_until);
+        }
+    }
+    /* ---- the sync block's IDLE / SYNC alternation (sync_impl.cc:73-134) */
+    struct Seen {
+        long long t, pos;
+    };
+    std::vector<Seen> seen;
+    long long pos = st0.sync_skip, next = n;
+    for (long long t : trig) {
+        if (t >= n) break;
+        if (t < pos) continue; /* inside the 111 samples the previous SYNC pass consumed */
+        if (t + 240 > n) {
+            if (!in->final) next = t;
+            break;
+        }
+        seen.push_back(Seen{ t, pos });
+        pos = t + 111;
+    }
+    if ((long long)seen.size() > (long long)out->sync_capacity)
+        return fail(ctx, W80211_E_CAPACITY, "detect_batch: sync_capacity %d < %zu triggers", out->sync_capacity, seen.size());
+    /* ---- per-trigger work on the GPU, plus one more record for the state at `next` */
+    const int nev = (int)seen.size() + 1;
+    RS(pin_reserve(ctx, g.h_ev, (size_t)nev * sizeof(w_det_event)));
+    RS(pin_reserve(ctx, g.h_dres, (size_t)nev * sizeof(w_det_result)));
+    RS(dev_reserve(ctx, g.det_ev, (size_t)nev * sizeof(w_det_event)));
+    RS(dev_reserve(ctx, g.det_res, (size_t)nev * sizeof(w_det_result)));
+    w_det_event* hev = (w_det_event*)g.h_ev.p;
+    size_t ri = 0; /* last run that starts before the event's sample */
+    auto last_run_before = [&](long long t) -> const Run* {
+        while (ri + 1 < runs.size() && runs[ri + 1].s < t) ri++;
+        return (!runs.empty() && runs[ri].s < t) ? &runs[ri] : nullptr;
+    };
+    for (int k = 0; k < nev; k++) {
+        const bool real = k + 1 < nev;
+        const long long t = real ? seen[(size_t)k].t : next;
+        const Run* r = last_run_before(t);
+        hev[k].rs = r ? r->s : 0;
+        hev[k].re = r ? std::min(r->e, t) : 0;
+        hev[k].pos = real ? seen[(size_t)k].pos : pos;
+        hev[k].t = t;
+        hev[k].do_sync = real ? 1 : 0;
+        hev[k].pad_ = 0;
+    }
+    CK(cudaMemcpyAsync(g.det_ev.p, hev, (size_t)nev * sizeof(w_det_event), cudaMemcpyHostToDevice, st));
+    w_launch_sync_events(st, nev, (const w_det_event*)g.det_ev.p, d_ac, d_cj, d_sg, st0.conj_ac, make_float2(st0.conj_re, st0.conj_im),
+                         (w_det_result*)g.det_res.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(g.h_dres.p, g.det_res.p, (size_t)nev * sizeof(w_det_result), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const w_det_result* hr = (const w_det_result*)g.h_dres.p;
+    int nsync = 0;
+    for (size_t k = 0; k < seen.size(); k++) {
+        if (!hr[k].valid) continue;
+        w80211_sync& sy = out->syncs[nsync++];
+        sy.pos = (uint64_t)(seen[k].t + hr[k].mindex);
+        sy.rad = hr[k].rad;
+        sy.snr = hr[k].snr;
+        sy.rssi = hr[k].rssi;
+        sy.flags = W80211_SYNC_TAGGED;
+    }
+    out->nsync = nsync;
+    out->n_trigger = (int32_t)seen.size();
+    out->next = (uint64_t)next;
+    /* ---- both blocks' state at `next` */
+    w80211_detect_state s1;
+    memset(&s1, 0, sizeof(s1));
+    const w_det_result& tail = hr[nev - 1];
+    s1.conj_re = tail.conj.x;
+    s1.conj_im = tail.conj.y;
+    for (const auto& r : runs) {
+        if (r.s < next && r.e >= next && next > 0) { /* sample next-1 is inside this run */
+            s1.n_plateau = (int32_t)std::min<long long>(next - r.s, 0x7fffffff);
+            s1.f_plateau_end = (r.fpe0 || (r.i0 >= 0 && r.i0 < next)) ? 1 : 0;
+            s1.conj_ac = tail.run_max;
+            break;
+        }
+    }
+    for (long long t : trig) {
+        if (t < next) continue;
+        if (t - 79 < next) s1.count_down = (int32_t)(t - next + 1);
+        break;
+    }
+    s1.sync_skip = (int32_t)std::max(0ll, pos - next);
+    out->state = next > 0 ? s1 : st0; /* next = 0: nothing was consumed */
+    ctx->stats.kernel_launches += 2;
+    return W80211_OK;
 }
 
 int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_signal_out* out)

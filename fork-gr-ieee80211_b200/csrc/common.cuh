@@ -185,6 +185,25 @@ struct w_sig_acc {
     int sync; /* row of chan_all */
     int pad_;
 };
+/* detection stage: one trigger flag the sync block acts on, and what comes back */
+struct w_det_event {
+    long long rs;  /* run whose 0x02 flags are the last before the trigger: start (negative: it began before this buffer) */
+    long long re;  /* ... end of the range to search (exclusive): min(run end, t) */
+    long long pos; /* where the sync block's IDLE scan began */
+    long long t;   /* the trigger flag's sample */
+    int do_sync;   /* 0: only the conj / run maximum are wanted (state at the end of the buffer) */
+    int pad_;
+};
+struct w_det_result {
+    float2 conj;
+    float run_max;
+    int valid, mindex;
+    float rad, snr, rssi;
+};
+void w_launch_run_edges(cudaStream_t st, const float* ac, unsigned long long n, int prev_above0, unsigned int cap,
+                        unsigned int* counters, unsigned int* starts, unsigned int* ends);
+void w_launch_sync_events(cudaStream_t st, int nev, const w_det_event* ev, const float* ac, const float2* conj, const float2* sig,
+                          float conj_ac0, float2 conj0, w_det_result* res);
 void w_launch_lsig(cudaStream_t st, const W80211Tables* tab, int nsync, const w80211_sync* syncs, const float2* iq0,
                    unsigned long long nsamples, int4* res, float2* chan_all);
 void w_launch_cfo_copy(cudaStream_t st, int npkt, int nant, int max_nsamp, const w_sig_acc* acc, const float2* in0,

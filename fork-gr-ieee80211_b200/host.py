@@ -20,6 +20,7 @@ SYMBOLS = [
     "w80211_abi_version", "w80211_sizeof", "w80211_create", "w80211_destroy", "w80211_last_error", "w80211_stats_get",
     "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
     "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free", "w80211_signal_batch",
+    "w80211_detect_batch",
 ]
 
 
@@ -77,6 +78,21 @@ class SignalOut(C.Structure):
                 ("lsig_ms", C.c_float), ("copy_ms", C.c_float)]
 
 
+class DetectState(C.Structure):
+    _fields_ = [("n_plateau", C.c_int32), ("f_plateau_end", C.c_int32), ("count_down", C.c_int32), ("conj_ac", C.c_float),
+                ("conj_re", C.c_float), ("conj_im", C.c_float), ("sync_skip", C.c_int32), ("reserved", C.c_int32)]
+
+
+class DetectIn(C.Structure):
+    _fields_ = [("mem", C.c_int32), ("final", C.c_int32), ("nsamples", C.c_uint64), ("preac", C.c_void_p),
+                ("preconj", C.c_void_p), ("sig", C.c_void_p), ("state", C.POINTER(DetectState))]
+
+
+class DetectOut(C.Structure):
+    _fields_ = [("nsync", C.c_int32), ("sync_capacity", C.c_int32), ("n_trigger", C.c_int32), ("reserved", C.c_int32),
+                ("next", C.c_uint64), ("syncs", C.c_void_p), ("state", DetectState)]
+
+
 class Stats(C.Structure):
     _fields_ = [("packets_in", C.c_uint64), ("packets_decoded", C.c_uint64), ("dropped_gate", C.c_uint64),
                 ("ndp", C.c_uint64), ("unsupported", C.c_uint64), ("bad_input", C.c_uint64),
@@ -120,6 +136,7 @@ def load():
         L.w80211_rx_collect.argtypes = [vp, C.c_int]
         L.w80211_rx_batch.argtypes = [vp, C.POINTER(BatchIn), C.POINTER(BatchOut)]
         L.w80211_signal_batch.argtypes = [vp, C.POINTER(SignalIn), C.POINTER(SignalOut)]
+        L.w80211_detect_batch.argtypes = [vp, C.POINTER(DetectIn), C.POINTER(DetectOut)]
         _lib = L
     return _lib
 
@@ -350,6 +367,27 @@ class Receiver:
         k, used = so.npkt, so.iq_used
         return {"iq": [x[:used] for x in out], "pkts": pk[:k].copy(), "chan": ch[:k].copy(), "sync_of_pkt": sop[:k].copy(),
                 "next": int(so.next), "need": int(so.need), "nsync_used": int(so.nsync_used), "n_rejected": int(so.n_rejected)}
+
+    def detect(self, preac, preconj, sig, state=None, final=True):
+        """presiso streams -> sync flags (w80211_detect_batch): what trigger + sync do.
+        Returns dict(syncs=SYNC_DTYPE array, next, state=DetectState, n_trigger)."""
+        preac = np.ascontiguousarray(preac, np.float32)
+        preconj = np.ascontiguousarray(preconj, np.complex64)
+        sig = np.ascontiguousarray(sig, np.complex64)
+        n = len(preac)
+        assert len(preconj) == n and len(sig) == n
+        di, do = DetectIn(), DetectOut()
+        di.mem, di.final, di.nsamples = MEM_HOST, int(bool(final)), n
+        di.preac, di.preconj, di.sig = preac.ctypes.data, preconj.ctypes.data, sig.ctypes.data
+        if state is not None:
+            di.state = C.pointer(state)
+        cap = n // 100 + 16
+        sy = np.zeros(cap, SYNC_DTYPE)
+        do.sync_capacity, do.syncs = cap, sy.ctypes.data
+        self._check(self.L.w80211_detect_batch(self.h, C.byref(di), C.byref(do)))
+        st = DetectState()
+        C.memmove(C.byref(st), C.byref(do.state), C.sizeof(DetectState))
+        return {"syncs": sy[:do.nsync].copy(), "next": int(do.next), "state": st, "n_trigger": int(do.n_trigger)}
 
     def stats(self):
         s = Stats()

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define W80211_ABI_VERSION 4
+#define W80211_ABI_VERSION 5
 
 /* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
 #define W80211_F_L 0
@@ -204,6 +204,39 @@ typedef struct w80211_signal_out {
     float lsig_ms, copy_ms;  /* out: CUDA-event durations of the two kernels of this call */
 } w80211_signal_out;
 
+/* ---- packet detection: trigger + sync ----------------------------------------------
+ * State of the reference's trigger block (lib/trigger_impl.h:38-43) and sync block (lib/sync_impl.h:40-52) between two
+ * buffers of one stream.  All zero for a new stream. */
+typedef struct w80211_detect_state {
+    int32_t n_plateau;     /* trigger: length of the current run of preac > 0.3 (d_nPlateau) */
+    int32_t f_plateau_end; /* trigger: this run has already started a countdown (d_fPlateauEnd) */
+    int32_t count_down;    /* trigger: samples until the pending trigger flag, 0 = none (d_fPlateau / d_countDown) */
+    float conj_ac;         /* trigger: largest preac of the current run (d_conjAc) */
+    float conj_re, conj_im; /* sync: d_conjMultiAvg, the preconj sample at the last 0x02 flag it saw */
+    int32_t sync_skip;     /* sync: leading samples of the next buffer that its SYNC state has already consumed */
+    int32_t reserved;
+} w80211_detect_state;
+
+typedef struct w80211_detect_in {
+    int32_t mem;           /* where preac / preconj / sig live */
+    int32_t final;         /* non-zero: no samples follow; a trigger closer than 240 samples to the end is dropped */
+    uint64_t nsamples;
+    const float* preac;    /* [nsamples] presiso output 0: |moving average 48 of x[n-16] conj(x[n])| / moving average 64 of |x|^2 */
+    const float* preconj;  /* [nsamples][2] presiso output 1: that complex moving average (examples/presiso.grc) */
+    const float* sig;      /* [nsamples][2] the received samples, aligned with the two streams above (examples/rx.grc:753-767) */
+    const w80211_detect_state* state; /* NULL = new stream */
+} w80211_detect_in;
+
+typedef struct w80211_detect_out {
+    int32_t nsync;         /* out: sync flags found, = entries written to syncs[] */
+    int32_t sync_capacity; /* entries syncs[] can hold */
+    int32_t n_trigger;     /* out: trigger flags (0x01) the sync block acted on */
+    int32_t reserved;
+    uint64_t next;         /* out: first sample the next call must start at (nsamples unless a trigger waits for samples) */
+    w80211_sync* syncs;    /* host: position, rad, snr, rssi of every flag, ascending: the input of w80211_signal_batch */
+    w80211_detect_state state; /* out: state at `next` */
+} w80211_detect_out;
+
 /* Timing of the last completed batch, measured with CUDA events on the ctx's own stream (ms). */
 typedef struct w80211_timing {
     float h2d, header, demod, viterbi, traceback, post, d2h, total;
@@ -214,7 +247,7 @@ typedef struct w80211_timing {
 
 int w80211_abi_version(void);
 /* sizeof of the ABI structs as compiled: 0 pkt_in, 1 batch_in, 2 desc, 3 mpdu, 4 batch_out, 5 stats, 6 timing, 7 cfg,
- * 8 sync, 9 signal_in, 10 signal_out
+ * 8 sync, 9 signal_in, 10 signal_out, 11 detect_state, 12 detect_in, 13 detect_out
  * (lets a binding written in another language check its own layout) */
 size_t w80211_sizeof(int what);
 int w80211_create(const w80211_cfg* cfg, w80211_ctx** out);
@@ -229,6 +262,14 @@ void* w80211_stream(const w80211_ctx* ctx, int slot);
  * full-speed DMA without linking the CUDA runtime itself.  NULL when the allocation fails. */
 void* w80211_host_alloc(size_t bytes);
 void w80211_host_free(void* p);
+
+/* presiso streams -> sync flags: what the trigger block (lib/trigger_impl.cc:60-117) and the sync block
+ * (lib/sync_impl.cc:61-196) do between presiso and signal.  The runs of preac > 0.3 are found in parallel; the host
+ * walks them the way the trigger's plateau / countdown logic and the sync block's IDLE / SYNC states would; one GPU
+ * thread per surviving trigger then repeats sync_impl::ltf_autoCorrelation and ltf_cfo with the reference's own
+ * sequential binary32 running sums.  Flag positions and rssi are exact; rad and snr go through atan2f / cosf / sinf /
+ * log10 and agree with a host libm to a few ulp.  Synchronous, on the signal stage's stream. */
+int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_detect_out* out);
 
 /* Raw samples + sync flags -> packets in demod's input format: what signal / signal2 do between sync and demod
  * (lib/signal_impl.cc:62-212, lib/signal2_impl.cc:62-222).  Every flag's L-SIG is demodulated and decoded in

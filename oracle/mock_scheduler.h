@@ -7,7 +7,8 @@
  *     for chunk_out output items; if the block makes no progress the window
  *     grows, like GR honouring forecast(), until all remaining input is visible;
  *   - tags are visible through get_tags_in_range() with absolute offsets;
- *   - output items returned are appended to the output stream.
+ *   - output items returned are appended to the output stream;
+ *   - with honor_forecast, noutput_items is halved until forecast() is satisfied by the visible input.
  * The run ends when the block makes no progress for MOCK_IDLE_STOP calls in a
  * row while seeing all the remaining input (the reference state machines take
  * up to four zero-progress calls between states).
@@ -24,7 +25,8 @@ inline long mock_run(block& b,
                      const std::vector<const mock_stream*>& ins,
                      const std::vector<mock_stream*>& outs,
                      long chunk_in,
-                     long chunk_out)
+                     long chunk_out,
+                     bool honor_forecast = false)
 {
     const size_t nin = ins.size(), nout = outs.size();
     b.mock_in = ins;
@@ -59,7 +61,20 @@ inline long mock_run(block& b,
             out_ptrs[o] = scratch[o].data();
         }
         std::fill(b.mock_consumed.begin(), b.mock_consumed.end(), 0);
-        int produced = b.general_work((int)win_out, ninput, in_ptrs, out_ptrs);
+        long call_out = win_out;
+        if (honor_forecast) {
+            /* like GR's single-threaded executor: shrink noutput_items until forecast() fits the visible input; blocks
+             * that index their input by noutput_items (trigger, sync) depend on it */
+            for (; call_out > 0; call_out /= 2) {
+                gr_vector_int need(nin, 0);
+                b.forecast((int)call_out, need);
+                bool fits = true;
+                for (size_t i = 0; i < nin; i++) fits = fits && need[i] <= ninput[i];
+                if (fits) break;
+            }
+            if (call_out == 0) break; /* starved: the flowgraph would end here */
+        }
+        int produced = b.general_work((int)call_out, ninput, in_ptrs, out_ptrs);
         calls++;
         bool progress = false;
         if (produced > 0) {

@@ -4,6 +4,8 @@
  * Test infrastructure only; it also hosts this repo's own drop-in blocks in
  * the block-level equivalence tests. */
 #pragma once
+#include <chrono>
+#include <iostream>
 #include <cstdint>
 #include <memory>
 #include <string>

@@ -24,6 +24,8 @@
 #include <gnuradio/ieee80211/signal.h>
 #include <gnuradio/ieee80211/signal2.h>
 #ifndef W80211_DRIVER_OURS
+#include <gnuradio/ieee80211/sync.h>
+#include <gnuradio/ieee80211/trigger.h>
 #include "cloud80211phy.h"
 #endif
 #include "mock_scheduler.h"
@@ -33,6 +35,7 @@ using gr::mock_stream;
 struct ref_block {
     std::shared_ptr<gr::block> blk;
     std::vector<std::vector<uint8_t>> msgs;
+    bool honor_forecast = false; /* trigger / sync index their input by noutput_items */
 };
 
 static std::string g_key_tmp;
@@ -111,6 +114,15 @@ ref_block* ref_block_new(const char* kind, int a0, int a1)
         b->blk = gr::ieee80211::signal::make();
     else if (k == "signal2")
         b->blk = gr::ieee80211::signal2::make();
+#ifndef W80211_DRIVER_OURS
+    else if (k == "trigger" || k == "sync") {
+        if (k == "trigger")
+            b->blk = gr::ieee80211::trigger::make();
+        else
+            b->blk = gr::ieee80211::sync::make();
+        b->honor_forecast = true;
+    }
+#endif
     else if (k == "demod")
         b->blk = gr::ieee80211::demod::make(a0, a1);
     else if (k == "demod2")
@@ -134,7 +146,7 @@ long ref_block_run(ref_block* b, mock_stream** ins, int nin, mock_stream** outs,
     for (int o = 0; o < nout; o++) vout.push_back(outs[o]);
     long calls;
     try {
-        calls = gr::mock_run(*b->blk, vin, vout, chunk_in, chunk_out);
+        calls = gr::mock_run(*b->blk, vin, vout, chunk_in, chunk_out, b->honor_forecast);
     } catch (const std::exception& e) {
         fprintf(stderr, "ref_block_run: exception: %s\n", e.what());
         return -1;

@@ -216,6 +216,22 @@ def run_signal(iq_list, sync_idx, rad=0.0, snr=0.0, rssi=0.0, chunk_in=0, chunk_
     return outs
 
 
+def run_trigger(preac, chunk_in=0, chunk_out=8192):
+    """presiso's autocorrelation stream -> the trigger block's flag stream (uint8: 0x01 trigger, 0x02 new maximum)."""
+    blk = Block("trigger")
+    out = Stream(itemsize=1)
+    blk.run([Stream(np.asarray(preac, np.float32))], out, chunk_in, chunk_out)
+    return out
+
+
+def run_sync(trigger_stream, preconj, sig, chunk_in=0, chunk_out=8192):
+    """trigger flags + presiso's conjugate stream + samples -> the sync block's flag stream with tags rad / snr / rssi."""
+    blk = Block("sync")
+    out = Stream(itemsize=1)
+    blk.run([trigger_stream, Stream(np.asarray(preconj, np.complex64)), Stream(np.asarray(sig, np.complex64))], out, chunk_in, chunk_out)
+    return out
+
+
 def run_demod(sig_streams, mupos=0, mugid=2, chunk_in=0, chunk_out=8192):
     """signal-format stream(s) -> LLR stream with demod's tags."""
     blk = Block("demod", mupos, mugid) if len(sig_streams) == 1 else Block("demod2")

@@ -81,3 +81,18 @@ def build_stream(batches, rads, gap=300, seed=0, noise=1e-3):
     tail = np.zeros(400, np.complex64)
     raw = [np.concatenate(x + [tail]) for x in parts]
     return raw, np.array(pos, np.int64), np.array(rr, np.float32)
+
+
+def presiso(x):
+    """examples/presiso.grc in numpy: preconj[n] = sum_{k<48} x[n-k-16] conj(x[n-k]), preac[n] = |preconj[n]| / sum_{k<64} |x[n-k]|^2
+    (samples before the start of the stream count as zero).  Both sides of a parity test are fed these same arrays."""
+    x = np.asarray(x, np.complex128)
+    n = len(x)
+    d = np.concatenate([np.zeros(16, complex), x[:n - 16]]) * np.conj(x)
+    c = np.concatenate([[0], np.cumsum(d)])
+    ma = c[1:] - np.concatenate([np.zeros(48, complex), c[1:n - 47]])[:n]
+    p = np.concatenate([[0], np.cumsum(np.abs(x) ** 2)])
+    pw = p[1:] - np.concatenate([np.zeros(64), p[1:n - 63]])[:n]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ac = (np.abs(ma).astype(np.float32) / pw.astype(np.float32)).astype(np.float32)
+    return ac, ma.astype(np.complex64)
