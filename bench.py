@@ -369,36 +369,66 @@ def main_gpu(args):
     e2e_bits, e2e_ms = e2e_leg(bi_host16)      # sc16 samples on the wire (4 B per sample): the headline host-fed figure
     clk = clocks.stop(t_from, t_to)
 
-    # ---- signal stage on resident raw samples: every packet's whole PPDU with its own carrier
-    # offset, 80 noise-free gap samples between packets, one sync flag per packet; output left in HBM and decoded once
+    # ---- front end (SURVEY.md 8(f) N3 + N1) on resident raw samples: every packet's whole PPDU with its own carrier offset,
+    # 320 empty samples between packets.  presiso -> detect (trigger + sync) -> signal (L-SIG check, CFO-corrected copy), all in
+    # HBM; the packets it hands over are then demodulated and decoded once.
+    P_full = P
+
     def signal_leg():
         ppdu = ub["ppdu"][0]
-        npp, gap = ppdu.shape[1], 80
+        P = min(P_full, nsm * 12 * 32 // 2)  # a quarter of the resident batch: these stages scale linearly, HBM is nearly full by now
+        reps = (P + N_UNIQUE - 1) // N_UNIQUE
+        npp, gap = ppdu.shape[1], 320
         stride = npp + gap
         rads = ((np.arange(N_UNIQUE) % 7 - 3) * 0.003).astype(np.float32)
         u = np.zeros((N_UNIQUE, stride), np.complex64)
         u[:, gap:] = (ppdu.astype(np.complex128) * np.exp(-1j * rads[:, None].astype(np.float64) * np.arange(npp)[None, :])).astype(np.complex64)
-        raw_dev = torch.empty(P * stride, dtype=torch.complex64, device=dev)
+        nraw = P * stride
+        raw_dev = torch.empty(nraw, dtype=torch.complex64, device=dev)
         usrc = torch.from_numpy(u.reshape(-1)).to(dev)
         for r in range(reps):
             n = min(N_UNIQUE, P - r * N_UNIQUE) * stride
             raw_dev[r * N_UNIQUE * stride: r * N_UNIQUE * stride + n] = usrc[:n]
-        sy = np.zeros(P, host.SYNC_DTYPE)
-        sy["pos"] = np.arange(P, dtype=np.uint64) * stride + gap + int(ub["sync_idx"])
-        sy["rad"] = np.tile(rads, reps)[:P]
-        sy["flags"] = host.SYNC_TAGGED
+        ac_dev = torch.empty(nraw, dtype=torch.float32, device=dev)
+        cj_dev = torch.empty(nraw, dtype=torch.complex64, device=dev)
+        KS = min(args.steps, 5)
+        torch.cuda.synchronize()
+        # presiso
+        for _ in range(2):
+            rx._check(L.w80211_presiso_batch(h, raw_dev.data_ptr(), nraw, host.MEM_DEVICE, ac_dev.data_ptr(), cj_dev.data_ptr()))
+        t0 = time.perf_counter()
+        for _ in range(KS):
+            rx._check(L.w80211_presiso_batch(h, raw_dev.data_ptr(), nraw, host.MEM_DEVICE, ac_dev.data_ptr(), cj_dev.data_ptr()))
+        pre_ms = (time.perf_counter() - t0) * 1e3 / KS
+        # trigger + sync
+        cap = 3 * P + 64
+        sy = np.zeros(cap, host.SYNC_DTYPE)
+        di, do = host.DetectIn(), host.DetectOut()
+        di.mem, di.final, di.nsamples = host.MEM_DEVICE, 1, nraw
+        di.preac, di.preconj, di.sig = ac_dev.data_ptr(), cj_dev.data_ptr(), raw_dev.data_ptr()
+        do.sync_capacity, do.syncs = cap, sy.ctypes.data
+        for _ in range(2):
+            rx._check(L.w80211_detect_batch(h, C.byref(di), C.byref(do)))
+        t0 = time.perf_counter()
+        for _ in range(KS):
+            rx._check(L.w80211_detect_batch(h, C.byref(di), C.byref(do)))
+        det_ms = (time.perf_counter() - t0) * 1e3 / KS
+        nflag, ntrig = int(do.nsync), int(do.n_trigger)
+        true_pos = np.arange(P, dtype=np.int64) * stride + gap + int(ub["sync_idx"])
+        found = sy[:nflag]
+        near = np.abs(found["pos"].astype(np.int64)[np.searchsorted(found["pos"].astype(np.int64), true_pos - 4).clip(0, max(nflag - 1, 0))] - true_pos) <= 4 \
+            if nflag else np.zeros(P, bool)
+        # signal stage on the detected flags
         out_iq = torch.empty(P * nsamp, dtype=torch.complex64, device=dev)
-        out_ch = torch.empty(P * 64, dtype=torch.complex64, device=dev)
-        pk_out = np.zeros(P, host.PKT_IN_DTYPE)
+        out_ch = torch.empty(max(nflag, 1) * 64, dtype=torch.complex64, device=dev)
+        pk_out = np.zeros(max(nflag, 1), host.PKT_IN_DTYPE)
         si, so = host.SignalIn(), host.SignalOut()
-        si.nsync, si.nant, si.mem, si.final = P, 1, host.MEM_DEVICE, 1
-        si.iq[0], si.nsamples, si.syncs, si.start = raw_dev.data_ptr(), P * stride, sy.ctypes.data, 0
+        si.nsync, si.nant, si.mem, si.final = nflag, 1, host.MEM_DEVICE, 1
+        si.iq[0], si.nsamples, si.syncs, si.start = raw_dev.data_ptr(), nraw, found.ctypes.data, 0
         so.mem, so.iq_capacity, so.pkts, so.chan = host.MEM_DEVICE, P * nsamp, pk_out.ctypes.data, out_ch.data_ptr()
         so.iq[0] = out_iq.data_ptr()
-        torch.cuda.synchronize()
         for _ in range(2):
             rx._check(L.w80211_signal_batch(h, C.byref(si), C.byref(so)))
-        KS = min(args.steps, 5)
         lsig = copy = 0.0
         t0 = time.perf_counter()
         for _ in range(KS):
@@ -407,14 +437,19 @@ def main_gpu(args):
             copy += so.copy_ms
         wall = (time.perf_counter() - t0) * 1e3 / KS
         npk_sig = int(so.npkt)
-        pk2 = torch.from_numpy(pk_out.view(np.uint8).copy()).to(dev)
-        bi2 = host.Receiver.make_in([out_iq.data_ptr()], pk2.data_ptr(), out_ch.data_ptr(), mem=host.MEM_DEVICE, nsamples=P * nsamp, npkt=P)
+        pk2 = torch.from_numpy(pk_out[:npk_sig].view(np.uint8).copy()).to(dev)
+        bi2 = host.Receiver.make_in([out_iq.data_ptr()], pk2.data_ptr(), out_ch.data_ptr(), mem=host.MEM_DEVICE,
+                                    nsamples=int(so.iq_used), npkt=npk_sig)
         _, ok2 = run_steps(1, bi2, bo_d, False)
         copy_bytes = float(npk_sig) * (nsamp * 16.0 + 1024.0)
-        return {"packets_per_step": P, "accepted": npk_sig, "fcs_ok_after_demod_decode": int(ok2), "ms_per_step_host_wall": wall,
-                "lsig_kernel_ms": lsig / KS, "cfo_copy_kernel_ms": copy / KS,
+        return {"packets_per_step": P, "raw_samples_per_step": nraw,
+                "presiso_ms_host_wall": pre_ms, "presiso_gbs": nraw * 20.0 / (pre_ms * 1e-3) / 1e9,
+                "detect_ms_host_wall": det_ms, "triggers": ntrig, "sync_flags": nflag, "true_packets_flagged": int(near.sum()),
+                "signal_ms_host_wall": wall, "lsig_kernel_ms": lsig / KS, "cfo_copy_kernel_ms": copy / KS,
                 "cfo_copy_gbs": copy_bytes / (copy / KS * 1e-3) / 1e9 if copy > 0 else None,
-                "note": "w80211_signal_batch, raw samples and results in HBM; not part of `value` (the north-star path starts at demod's input)"}
+                "accepted": npk_sig, "fcs_ok_after_demod_decode": int(ok2),
+                "note": "w80211_presiso_batch + w80211_detect_batch + w80211_signal_batch, raw samples and results in HBM; not part of "
+                        "`value` (the north-star path starts at demod's input)"}
 
     sig_stage = signal_leg() if world == 1 else None
     h2d = PE * nsamp * 4 + pk_host.numel() + ch_host.numel() * 4

@@ -21,6 +21,7 @@
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -71,7 +72,7 @@ struct SigStage {
     DevBuf iq[2], syncs, res, chan_all, acc, out_iq[2], out_chan;
     PinBuf h_res, h_acc;
     /* detection stage */
-    DevBuf det_ac, det_conj, det_sig, det_cnt, det_starts, det_ends, det_ev, det_res;
+    DevBuf det_ac, det_conj, det_sig, det_cnt, det_starts, det_ends, det_sorted, det_tmp, det_ev, det_res;
     PinBuf h_edges, h_ev, h_dres;
 };
 
@@ -624,7 +625,7 @@ void w80211_destroy(w80211_ctx* ctx)
     {
         SigStage& g = ctx->sig;
         DevBuf* db[] = {&g.iq[0], &g.iq[1], &g.syncs, &g.res, &g.chan_all, &g.acc, &g.out_iq[0], &g.out_iq[1], &g.out_chan,
-                        &g.det_ac, &g.det_conj, &g.det_sig, &g.det_cnt, &g.det_starts, &g.det_ends, &g.det_ev, &g.det_res};
+                        &g.det_ac, &g.det_conj, &g.det_sig, &g.det_cnt, &g.det_starts, &g.det_ends, &g.det_sorted, &g.det_tmp, &g.det_ev, &g.det_res};
         for (DevBuf* b : db)
             if (b->p) cudaFree(b->p);
         if (g.h_res.p) cudaFreeHost(g.h_res.p);
@@ -707,6 +708,36 @@ int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out
     return w80211_rx_collect(ctx, 0);
 }
 
+int w80211_presiso_batch(w80211_ctx* ctx, const float* sig, uint64_t nsamples, int32_t mem, float* preac, float* preconj)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (nsamples > 0 && (!sig || !preac || !preconj)) return fail(ctx, W80211_E_ARG, "bad presiso_batch arguments");
+    if (nsamples == 0) return W80211_OK;
+    CK(cudaSetDevice(ctx->device));
+    SigStage& g = ctx->sig;
+    if (!g.stream) {
+        CK(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+        for (auto& e : g.ev) CK(cudaEventCreate(&e));
+    }
+    cudaStream_t st = g.stream;
+    if (mem == W80211_MEM_DEVICE) {
+        w_launch_presiso(st, (const float2*)sig, nsamples, preac, (float2*)preconj);
+        CK(cudaGetLastError());
+    } else {
+        RS(dev_reserve(ctx, g.det_sig, (size_t)nsamples * 8 + 64));
+        RS(dev_reserve(ctx, g.det_ac, (size_t)nsamples * 4 + 64));
+        RS(dev_reserve(ctx, g.det_conj, (size_t)nsamples * 8 + 64));
+        CK(cudaMemcpyAsync(g.det_sig.p, sig, (size_t)nsamples * 8, cudaMemcpyHostToDevice, st));
+        w_launch_presiso(st, (const float2*)g.det_sig.p, nsamples, (float*)g.det_ac.p, (float2*)g.det_conj.p);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(preac, g.det_ac.p, (size_t)nsamples * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(preconj, g.det_conj.p, (size_t)nsamples * 8, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    ctx->stats.kernel_launches += 1;
+    return W80211_OK;
+}
+
 int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_detect_out* out)
 {
     if (!ctx) return W80211_E_ARG;
@@ -719,6 +750,12 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
     if (st0.n_plateau < 0 || st0.count_down < 0 || st0.count_down > 80 || st0.sync_skip < 0)
         return fail(ctx, W80211_E_ARG, "detect_batch: impossible carried state");
     const long long n = (long long)in->nsamples;
+    static const bool trace = getenv("W80211_TRACE") != nullptr;
+    auto tnow = [] { return std::chrono::steady_clock::now(); };
+    auto tms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    const auto tt0 = tnow();
     out->nsync = out->n_trigger = 0;
     out->next = in->nsamples;
     out->state = st0;
@@ -744,28 +781,36 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
         d_cj = (const float2*)g.det_conj.p;
         d_sg = (const float2*)g.det_sig.p;
     }
-    /* ---- runs of preac > 0.3 */
-    const unsigned int cap = (unsigned int)(n / 2 + 2);
+    /* ---- runs of preac > 0.3: count the edges, then list them */
     RS(dev_reserve(ctx, g.det_cnt, 16));
-    RS(dev_reserve(ctx, g.det_starts, (size_t)cap * 4));
-    RS(dev_reserve(ctx, g.det_ends, (size_t)cap * 4));
-    CK(cudaMemsetAsync(g.det_cnt.p, 0, 16, st));
-    w_launch_run_edges(st, d_ac, (unsigned long long)n, st0.n_plateau > 0, cap, (unsigned int*)g.det_cnt.p, (unsigned int*)g.det_starts.p,
-                       (unsigned int*)g.det_ends.p);
-    CK(cudaGetLastError());
     RS(pin_reserve(ctx, g.h_edges, 16));
+    CK(cudaMemsetAsync(g.det_cnt.p, 0, 16, st));
+    w_launch_run_edges(st, d_ac, (unsigned long long)n, st0.n_plateau > 0, 0, (unsigned int*)g.det_cnt.p, nullptr, nullptr);
+    CK(cudaGetLastError());
     CK(cudaMemcpyAsync(g.h_edges.p, g.det_cnt.p, 16, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     const unsigned int ns = ((unsigned int*)g.h_edges.p)[0], ne = ((unsigned int*)g.h_edges.p)[1];
-    if (ns > cap || ne > cap) return fail(ctx, W80211_E_STATE, "detect_batch: edge list overflow");
+    RS(dev_reserve(ctx, g.det_starts, (size_t)ns * 4 + 16));
+    RS(dev_reserve(ctx, g.det_ends, (size_t)ne * 4 + 16));
+    CK(cudaMemsetAsync(g.det_cnt.p, 0, 16, st));
+    w_launch_run_edges(st, d_ac, (unsigned long long)n, st0.n_plateau > 0, std::max(ns, ne), (unsigned int*)g.det_cnt.p,
+                       (unsigned int*)g.det_starts.p, (unsigned int*)g.det_ends.p);
+    CK(cudaGetLastError());
     RS(pin_reserve(ctx, g.h_edges, (size_t)(ns + ne) * 4 + 16));
     unsigned int* hs = (unsigned int*)g.h_edges.p;
     unsigned int* he = hs + ns;
-    if (ns) CK(cudaMemcpyAsync(hs, g.det_starts.p, (size_t)ns * 4, cudaMemcpyDeviceToHost, st));
-    if (ne) CK(cudaMemcpyAsync(he, g.det_ends.p, (size_t)ne * 4, cudaMemcpyDeviceToHost, st));
+    {
+        const size_t tb = w_sort_u32_temp_bytes((int)std::max(ns, ne));
+        RS(dev_reserve(ctx, g.det_tmp, tb + 16));
+        RS(dev_reserve(ctx, g.det_sorted, (size_t)(ns + ne) * 4 + 16));
+        unsigned int* ds = (unsigned int*)g.det_sorted.p;
+        w_sort_u32(st, g.det_tmp.p, tb, (const unsigned int*)g.det_starts.p, ds, (int)ns);
+        w_sort_u32(st, g.det_tmp.p, tb, (const unsigned int*)g.det_ends.p, ds + ns, (int)ne);
+        CK(cudaGetLastError());
+        if (ns + ne) CK(cudaMemcpyAsync(hs, ds, (size_t)(ns + ne) * 4, cudaMemcpyDeviceToHost, st));
+    }
     CK(cudaStreamSynchronize(st));
-    std::sort(hs, hs + ns);
-    std::sort(he, he + ne);
+    const auto tt1 = tnow();
     struct Run {
         long long s, e; /* [s, e): s < 0 when the run began before this buffer, e = n when it is still open */
         long long i0;   /* sample at which this run started a countdown, -1: none */
@@ -835,12 +880,17 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
         hev[k].do_sync = real ? 1 : 0;
         hev[k].pad_ = 0;
     }
+    const auto tt2 = tnow();
     CK(cudaMemcpyAsync(g.det_ev.p, hev, (size_t)nev * sizeof(w_det_event), cudaMemcpyHostToDevice, st));
     w_launch_sync_events(st, nev, (const w_det_event*)g.det_ev.p, d_ac, d_cj, d_sg, st0.conj_ac, make_float2(st0.conj_re, st0.conj_im),
                          (w_det_result*)g.det_res.p);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(g.h_dres.p, g.det_res.p, (size_t)nev * sizeof(w_det_result), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    const auto tt3 = tnow();
+    if (trace)
+        fprintf(stderr, "detect_batch: edges %.2f ms (%u starts), host walk %.2f ms, events %.2f ms (%d)\n", tms(tt0, tt1), ns, tms(tt1, tt2),
+                tms(tt2, tt3), nev);
     const w_det_result* hr = (const w_det_result*)g.h_dres.p;
     int nsync = 0;
     for (size_t k = 0; k < seen.size(); k++) {
@@ -876,7 +926,7 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
     }
     s1.sync_skip = (int32_t)std::max(0ll, pos - next);
     out->state = next > 0 ? s1 : st0; /* next = 0: nothing was consumed */
-    ctx->stats.kernel_launches += 2;
+    ctx->stats.kernel_launches += 3;
     return W80211_OK;
 }
 

@@ -204,6 +204,9 @@ void w_launch_run_edges(cudaStream_t st, const float* ac, unsigned long long n, 
                         unsigned int* counters, unsigned int* starts, unsigned int* ends);
 void w_launch_sync_events(cudaStream_t st, int nev, const w_det_event* ev, const float* ac, const float2* conj, const float2* sig,
                           float conj_ac0, float2 conj0, w_det_result* res);
+size_t w_sort_u32_temp_bytes(int n);
+void w_sort_u32(cudaStream_t st, void* temp, size_t temp_bytes, const unsigned int* in, unsigned int* out, int n);
+void w_launch_presiso(cudaStream_t st, const float2* x, unsigned long long n, float* ac, float2* cj);
 void w_launch_lsig(cudaStream_t st, const W80211Tables* tab, int nsync, const w80211_sync* syncs, const float2* iq0,
                    unsigned long long nsamples, int4* res, float2* chan_all);
 void w_launch_cfo_copy(cudaStream_t st, int npkt, int nant, int max_nsamp, const w_sig_acc* acc, const float2* in0,

@@ -14,6 +14,7 @@
  * Every per-trigger result depends on at most a few hundred samples, so a thread per trigger keeps the reference's
  * operation order (bit-exact sums) and the batch supplies the parallelism.
  */
+#include <cub/device/device_radix_sort.cuh>
 #include "common.cuh"
 
 __device__ __forceinline__ bool above_thr(float v) { return v > 0.3f; }
@@ -167,4 +168,78 @@ void w_launch_sync_events(cudaStream_t st, int nev, const w_det_event* ev, const
 {
     if (nev <= 0) return;
     sync_event_kernel<<<(nev + 63) / 64, 64, 0, st>>>(nev, ev, ac, conj, sig, conj_ac0, conj0, res);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * examples/presiso.grc: the two streams the trigger and sync blocks read.
+ *   preconj[n] = sum_{k<48} x[n-16-k] * conj(x[n-k])          (delay 16, multiply conjugate, moving average 48)
+ *   preac[n]   = |preconj[n]| / sum_{k<64} |x[n-k]|^2         (complex to mag; mag squared, moving average 64; divide)
+ * Samples before the start of the buffer count as zero.  The reference has no source for this stage (a GRC hierarchy
+ * of stock GNU Radio blocks whose moving averages are running binary32 sums over the whole stream), so results are
+ * defined to the 1e-4 tolerance against a binary64 evaluation, not bit for bit.
+ * One thread produces PRE_SPAN consecutive outputs: the first by summing its windows, the rest by sliding them, from a
+ * shared-memory tile of the block's samples. */
+#define PRE_SPAN 8
+#define PRE_SHIFT 3 /* log2(PRE_SPAN) */
+#define PRE_THREADS 128
+#define PRE_TILE (PRE_SPAN * PRE_THREADS)
+__global__ void __launch_bounds__(PRE_THREADS) presiso_kernel(const float2* __restrict__ x, unsigned long long n,
+                                                              float* __restrict__ ac, float2* __restrict__ cj)
+{
+    /* one pad element per PRE_SPAN samples: the lanes of a warp are PRE_SPAN samples apart, PRE_SPAN + 1 elements apart in
+     * shared memory */
+#define T_(i) tile[(i) + ((i) >> PRE_SHIFT)]
+    __shared__ float2 tile[PRE_TILE + 80 + (PRE_TILE + 80) / PRE_SPAN + 1];
+    const long long base = (long long)blockIdx.x * PRE_TILE;
+    for (int i = threadIdx.x; i < PRE_TILE + 80; i += PRE_THREADS) {
+        const long long g = base - 80 + i;
+        T_(i) = (g >= 0 && g < (long long)n) ? __ldg(x + g) : make_float2(0.f, 0.f);
+    }
+    __syncthreads();
+    const int o = threadIdx.x * PRE_SPAN + 80; /* tile index of this thread's first output sample */
+    float sr = 0.f, si = 0.f, pw = 0.f;
+    for (int k = 47; k >= 0; k--) { /* oldest first */
+        const float2 a = T_(o - 16 - k), b = T_(o - k);
+        sr += a.x * b.x + a.y * b.y;
+        si += a.y * b.x - a.x * b.y;
+    }
+    for (int k = 63; k >= 0; k--) {
+        const float2 b = T_(o - k);
+        pw += b.x * b.x + b.y * b.y;
+    }
+#pragma unroll
+    for (int j = 0; j < PRE_SPAN; j++) {
+        const long long g = base + threadIdx.x * PRE_SPAN + j;
+        if (g < (long long)n) {
+            ac[g] = sqrtf(sr * sr + si * si) / pw;
+            cj[g] = make_float2(sr, si);
+        }
+        /* slide both windows by one sample */
+        if (j + 1 < PRE_SPAN) {
+            const int m = o + j + 1;
+            const float2 na = T_(m - 16), nb = T_(m), oa = T_(m - 64), ob = T_(m - 48), op = T_(m - 64);
+            sr += (na.x * nb.x + na.y * nb.y) - (oa.x * ob.x + oa.y * ob.y);
+            si += (na.y * nb.x - na.x * nb.y) - (oa.y * ob.x - oa.x * ob.y);
+            pw += (nb.x * nb.x + nb.y * nb.y) - (op.x * op.x + op.y * op.y);
+        }
+    }
+}
+#undef T_
+
+void w_launch_presiso(cudaStream_t st, const float2* x, unsigned long long n, float* ac, float2* cj)
+{
+    if (n == 0) return;
+    presiso_kernel<<<(unsigned int)((n + PRE_TILE - 1) / PRE_TILE), PRE_THREADS, 0, st>>>(x, n, ac, cj);
+}
+
+/* the edge lists come out of the atomics in arbitrary order: radix sort them on the device (a few 10^4 keys) */
+size_t w_sort_u32_temp_bytes(int n)
+{
+    size_t b = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, b, (const unsigned int*)nullptr, (unsigned int*)nullptr, n);
+    return b;
+}
+void w_sort_u32(cudaStream_t st, void* temp, size_t temp_bytes, const unsigned int* in, unsigned int* out, int n)
+{
+    if (n > 0) cub::DeviceRadixSort::SortKeys(temp, temp_bytes, in, out, n, 0, 32, st);
 }

@@ -20,7 +20,7 @@ SYMBOLS = [
     "w80211_abi_version", "w80211_sizeof", "w80211_create", "w80211_destroy", "w80211_last_error", "w80211_stats_get",
     "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
     "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free", "w80211_signal_batch",
-    "w80211_detect_batch",
+    "w80211_detect_batch", "w80211_presiso_batch",
 ]
 
 
@@ -137,6 +137,7 @@ def load():
         L.w80211_rx_batch.argtypes = [vp, C.POINTER(BatchIn), C.POINTER(BatchOut)]
         L.w80211_signal_batch.argtypes = [vp, C.POINTER(SignalIn), C.POINTER(SignalOut)]
         L.w80211_detect_batch.argtypes = [vp, C.POINTER(DetectIn), C.POINTER(DetectOut)]
+        L.w80211_presiso_batch.argtypes = [vp, vp, C.c_uint64, C.c_int32, vp, vp]
         _lib = L
     return _lib
 
@@ -367,6 +368,14 @@ class Receiver:
         k, used = so.npkt, so.iq_used
         return {"iq": [x[:used] for x in out], "pkts": pk[:k].copy(), "chan": ch[:k].copy(), "sync_of_pkt": sop[:k].copy(),
                 "next": int(so.next), "need": int(so.need), "nsync_used": int(so.nsync_used), "n_rejected": int(so.n_rejected)}
+
+    def presiso(self, sig):
+        """samples -> (preac, preconj) on the GPU (w80211_presiso_batch): examples/presiso.grc."""
+        sig = np.ascontiguousarray(sig, np.complex64)
+        ac = np.zeros(len(sig), np.float32)
+        cj = np.zeros(len(sig), np.complex64)
+        self._check(self.L.w80211_presiso_batch(self.h, sig.ctypes.data, len(sig), MEM_HOST, ac.ctypes.data, cj.ctypes.data))
+        return ac, cj
 
     def detect(self, preac, preconj, sig, state=None, final=True):
         """presiso streams -> sync flags (w80211_detect_batch): what trigger + sync do.

@@ -263,6 +263,13 @@ void* w80211_stream(const w80211_ctx* ctx, int slot);
 void* w80211_host_alloc(size_t bytes);
 void w80211_host_free(void* p);
 
+/* Received samples -> the two presiso streams (examples/presiso.grc: delay 16, multiply conjugate, moving averages of 48
+ * and 64, magnitude, divide), sig / preac / preconj all in `mem`.  Samples before sig[0] count as zero: a streaming caller
+ * overlaps consecutive buffers by 79 samples or more and ignores the first 79 outputs.  The reference holds no source for
+ * this stage (stock GNU Radio blocks with running binary32 sums), so the result is defined to 1e-4 relative against a
+ * binary64 evaluation.  Synchronous, on the signal stage's stream. */
+int w80211_presiso_batch(w80211_ctx* ctx, const float* sig, uint64_t nsamples, int32_t mem, float* preac, float* preconj);
+
 /* presiso streams -> sync flags: what the trigger block (lib/trigger_impl.cc:60-117) and the sync block
  * (lib/sync_impl.cc:61-196) do between presiso and signal.  The runs of preac > 0.3 are found in parallel; the host
  * walks them the way the trigger's plateau / countdown logic and the sync block's IDLE / SYNC states would; one GPU

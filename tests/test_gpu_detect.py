@@ -108,3 +108,20 @@ def test_detect_empty_silence_and_bad_arguments(rx):
     bad.count_down = 500
     with pytest.raises(host.W80211Error):
         rx.detect(one, z, z, state=bad)
+
+
+def test_presiso_on_the_gpu(refgr, rx):
+    """The GPU's presiso streams against the binary64 evaluation (1e-4 of the local scale), and the flags they lead to
+    against the reference blocks fed the numpy streams: same packets, positions within one sample."""
+    bs, raw, pos, rad = stream_of(31)
+    x = raw[0]
+    ac64, cj64 = presiso(x)
+    ac, cj = rx.presiso(x)
+    ok = np.isfinite(ac64) & (np.arange(len(x)) >= 80)
+    assert np.all(np.abs(cj[ok] - cj64[ok]) <= 1e-4 * np.maximum(np.abs(cj64[ok]), 1e-3 * np.abs(cj64).max()))
+    assert np.all(np.abs(ac[ok] - ac64[ok]) <= 1e-4 * np.maximum(ac64[ok], 1e-2))
+    ref, _, _ = ref_detect(refgr, ac64, cj64, x)
+    mine = rx.detect(ac, cj, x)["syncs"]
+    assert len(mine) == len(ref) == len(pos)
+    for s, (o, t) in zip(mine, ref):
+        assert abs(int(s["pos"]) - o) <= 1 and abs(float(s["rad"]) - t["rad"]) <= 1e-4
