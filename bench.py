@@ -351,6 +351,14 @@ def main_gpu(args):
     torch.cuda.synchronize()
     t_to = clocks.mark()
     launches = counters["launches"] * args.steps // KSEQ
+    if args.resident_only:
+        print(json.dumps({"value": bits / (ms * 1e-3) / 1e9, "ms_per_step": ms / args.steps, "packets": P, "lib": os.environ.get("W80211_LIB"),
+                          "fcs_ok_per_step": npk_ok / args.steps, "clocks": clocks.stop(t_from, t_to),
+                          "stage_ms_per_step": {k: round(v / KSEQ, 4) for k, v in stage.items()}}))
+        rx.close()
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
 
     # ---- end-to-end legs: pinned host buffers -> C ABI -> pinned host results, two slots in flight
     def e2e_leg(bi):
@@ -567,6 +575,7 @@ def main():
     ap.add_argument("--mpdu-len", type=int, default=4088, help="profiling only: shorter packets; the reported workload is the default")
     ap.add_argument("--ref-packets", type=int, default=512, help="packets per core and step for the CPU reference")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--resident-only", action="store_true", help="tuning runs: the resident leg and the per-kernel times only, short JSON line")
     args = ap.parse_args()
     global MPDU_LEN
     MPDU_LEN = args.mpdu_len

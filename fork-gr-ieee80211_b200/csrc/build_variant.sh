@@ -6,7 +6,7 @@ set -e
 cd "$(dirname "$0")"
 name=$1; shift
 mkdir -p ../variants /tmp/w80211_$name
-for f in hdr demod viterbi post iqconv capi; do
+for f in hdr demod viterbi post iqconv detect capi; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC -Xcudafe --diag_suppress=177 -Xcudafe --diag_suppress=20091 "$@" -c $f.cu -o /tmp/w80211_$name/$f.o &
 done
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Xcompiler -fPIC -x cu -c tables.cc -o /tmp/w80211_$name/tables.o &

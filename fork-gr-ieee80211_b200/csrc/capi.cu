@@ -302,7 +302,7 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
     RS(pin_reserve(ctx, s.h_mpdus, (size_t)internal_cap * sizeof(w80211_mpdu)));
     RS(pin_reserve(ctx, s.h_counters, 64));
     s.mpdu_cap = internal_cap;
-    w_launch_post(st, s.ndec, (const int4*)s.grp.p, (const int*)s.pkt_slot.p, (const int*)s.dec_list.p,
+    w_launch_post(st, ctx->d_tab, s.ndec, (const int4*)s.grp.p, (const int*)s.pkt_slot.p, (const int*)s.dec_list.p,
                   (const w80211_desc*)s.desc.p, (const uint32_t*)s.bits.p, (const uint32_t*)s.psdu_off.p, (uint8_t*)s.bytes.p,
                   (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
     CK(cudaGetLastError());

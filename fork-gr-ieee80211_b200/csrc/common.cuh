@@ -21,6 +21,7 @@
 #define W_WARP 32
 #define W_NMAPS 19
 #define W_MAPLEN 416
+#define W_XPOW8 4224
 
 /* Constant tables, generated on the host from the 802.11 formulas (tables.cc)
  * and kept in device global memory. */
@@ -36,6 +37,10 @@ struct W80211Tables {
      * 0..3 legacy nbpscs 1,2,4,6; 4..8 HT/VHT one stream nbpscs 1,2,4,6,8;
      * 9..13 two streams, stream 1 (deinterleave + stream de-parse); 14..18 stream 2. */
     uint16_t map[W_NMAPS][W_MAPLEN];
+    /* CRC-32 (reflected 0xEDB88320) for post.cu: slice-by-4 tables (crc_tab[0] is the byte table) and x^(2^k) mod P */
+    uint32_t crc_tab[4][256];
+    uint32_t crc_x2n[32];
+    uint32_t crc_xpow8[W_XPOW8]; /* x^(8n) mod P, n = 0 .. W_XPOW8-1 bytes */
 };
 
 struct cf32 {
@@ -217,6 +222,6 @@ int w_launch_viterbi(cudaStream_t st, const int* cr_first, const int4* grp, cons
                      const float* llr, uint2* surv);
 void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
                         const uint2* surv, uint32_t* bits);
-void w_launch_post(cudaStream_t st, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,
+void w_launch_post(cudaStream_t st, const W80211Tables* tab, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,
                    const w80211_desc* desc, const uint32_t* bits, const uint32_t* psdu_off, uint8_t* out_bytes,
                    w80211_mpdu* mpdus, unsigned int mpdu_cap, unsigned int* counters);

@@ -22,6 +22,22 @@
 #define DEMOD_GROUPS (DEMOD_THREADS / 8)
 #define DEMOD_SPC 8        /* symbols per work item (one 8-lane group walks them in order) */
 #define DEMOD_STAGE 832    /* floats: largest nCBPS (2 streams of 256-QAM) */
+#define DEMOD_PAD 2        /* floats after a group's staging row: rows start 2 banks apart (the deinterleaved positions of the
+                              8 bins a group writes at a time fall on 8 banks that repeat every row of 416 / 832 floats), and
+                              the pad is the slot that bins without data write to */
+#define DEMOD_MAPPAD 8     /* map entries after a table, all pointing at that slot */
+#ifndef DEMOD_NOHOIST
+#define DEMOD_NOHOIST 1
+#endif
+#ifndef DEMOD_HOIST
+#define DEMOD_HOIST 2
+#endif
+#ifndef DEMOD_EQHOIST
+#define DEMOD_EQHOIST 0
+#endif
+#ifndef DEMOD_BRANCHFREE
+#define DEMOD_BRANCHFREE 1
+#endif
 
 /* item -> packet: prefix[p] <= w < prefix[p+1].  Batches are mostly homogeneous, so an
  * interpolated guess is tried before the binary search. */
@@ -76,31 +92,60 @@ __device__ __forceinline__ void qam_llr(cf32 q, const uint16_t* __restrict__ map
     axis_llr<(NB >> 1)>(q.y, map + (NB >> 1), out);
 }
 
-/* a / f with y = RN(1/f); unsafe divisors and tiny quotients (where the FMA residual could leave the normal range) take
- * the plain division */
-__device__ __forceinline__ cf32 c_divf_known(cf32 a, float f, float y, bool slow)
+/* The LLRs of one symbol: q = eq * conj(pilot sum) / |pilot sum| per data subcarrier, demapped and scattered into the
+ * group's staging block in coded-bit order.  No branch per bin: a bin without data takes the table's pad entries and
+ * lands in the row's pad slot.  q = a / pa goes through y = RN(1/pa) (f_div_known); unsafe divisors and tiny quotients
+ * (where the FMA residual could leave the normal range) are found per symbol, not per bin, and the whole symbol is then
+ * redone with the plain division. */
+template <int NB, bool MIMO, bool SLOW>
+__device__ __forceinline__ bool symbol_llrs_pass(const cf32 (&e1)[8], const cf32 (&e2)[8], const int (&jj)[8], bool two, cf32 ps, float pa,
+                                                 float rpa, const uint16_t* __restrict__ map1, const uint16_t* __restrict__ map2,
+                                                 float* __restrict__ stg)
 {
-    const float qx = f_div_known(a.x, f, y), qy = f_div_known(a.y, f, y);
-    if (slow || !(fabsf(qx) >= 1e-30f && fabsf(qy) >= 1e-30f)) return c_divf(a, f);
-    return c_make(qx, qy);
+    bool bad = false;
+#pragma unroll
+    for (int k2 = 0; k2 < 8; k2++) {
+        const int j = jj[k2];
+#if DEMOD_BRANCHFREE
+        const int mo = j >= 0 ? j * NB : W_MAPLEN;
+#else
+        const int mo = j * NB;
+        if (j < 0) continue;
+#endif
+        {
+            const cf32 a = c_mul(e1[k2], ps);
+            const cf32 q = SLOW ? c_divf(a, pa) : c_make(f_div_known(a.x, pa, rpa), f_div_known(a.y, pa, rpa));
+            if (!SLOW) bad = bad || (j >= 0 && !(fabsf(q.x) >= 1e-30f && fabsf(q.y) >= 1e-30f));
+            qam_llr<NB>(q, map1 + mo, stg);
+        }
+        if (MIMO && two) {
+            const cf32 a = c_mul(e2[k2], ps);
+            const cf32 q = SLOW ? c_divf(a, pa) : c_make(f_div_known(a.x, pa, rpa), f_div_known(a.y, pa, rpa));
+            if (!SLOW) bad = bad || (j >= 0 && !(fabsf(q.x) >= 1e-30f && fabsf(q.y) >= 1e-30f));
+            qam_llr<NB>(q, map2 + mo, stg);
+        }
+    }
+    return bad;
 }
 
-/* the LLRs of one symbol: q = eq * conj(pilot sum) / |pilot sum| per data subcarrier, demapped and scattered into the
- * group's staging block in coded-bit order */
 template <int NB, bool MIMO>
 __device__ __forceinline__ void symbol_llrs(const cf32 (&e1)[8], const cf32 (&e2)[8], const int (&jj)[8], bool two, cf32 ps, float pa,
                                             const uint16_t* __restrict__ map1, const uint16_t* __restrict__ map2, float* __restrict__ stg)
 {
     const bool slow_pa = f_recip_unsafe(pa) || !(pa > 1e-30f) || !(pa < 1e30f);
     const float rpa = __frcp_rn(pa);
-#pragma unroll
-    for (int k2 = 0; k2 < 8; k2++) {
-        const int j = jj[k2];
-        if (j >= 0) {
-            qam_llr<NB>(c_divf_known(c_mul(e1[k2], ps), pa, rpa, slow_pa), map1 + j * NB, stg);
-            if (MIMO && two) qam_llr<NB>(c_divf_known(c_mul(e2[k2], ps), pa, rpa, slow_pa), map2 + j * NB, stg);
-        }
-    }
+#if DEMOD_HOIST == 2
+    bool redo = slow_pa;
+    if (!slow_pa) redo = symbol_llrs_pass<NB, MIMO, false>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
+    if (redo) symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
+#elif DEMOD_HOIST == 1
+    if (slow_pa)
+        symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
+    else if (symbol_llrs_pass<NB, MIMO, false>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg))
+        symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
+#else
+    symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
+#endif
 }
 
 __device__ __forceinline__ float shfl_f(float v, int src) { return __shfl_sync(0xffffffffu, v, src); }
@@ -111,8 +156,9 @@ __device__ __forceinline__ void load_sym(const float2* __restrict__ src, int g, 
     for (int n1 = 0; n1 < 8; n1++) v[n1] = valid ? __ldg(&src[8 * n1 + g]) : make_float2(0.f, 0.f);
 }
 
-/* FFT of samples already in registers (same arithmetic as fft64_lane8) */
-__device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, float* re, float* im, const float* wr, const float* wi)
+/* FFT of samples already in registers (same arithmetic as fft64_lane8); the lane's twiddles W64^(g*k1) come from the
+ * block's shared copy instead of sixteen registers per thread */
+__device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, float* re, float* im, const float2* __restrict__ tw /* [g][9] */)
 {
 #pragma unroll
     for (int n1 = 0; n1 < 8; n1++) {
@@ -123,9 +169,10 @@ __device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, 
     if (g) {
 #pragma unroll
         for (int k1 = 1; k1 < 8; k1++) {
+            const float2 w = tw[g * 9 + k1];
             float ar = re[k1], ai = im[k1];
-            re[k1] = C8_SUB(C8_MUL(ar, wr[k1]), C8_MUL(ai, wi[k1]));
-            im[k1] = C8_ADD(C8_MUL(ar, wi[k1]), C8_MUL(ai, wr[k1]));
+            re[k1] = C8_SUB(C8_MUL(ar, w.x), C8_MUL(ai, w.y));
+            im[k1] = C8_ADD(C8_MUL(ar, w.y), C8_MUL(ai, w.x));
         }
     }
 #pragma unroll
@@ -145,9 +192,10 @@ __device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, 
 template <bool MIMO>
 struct DemodSmem {
     double eqr[DEMOD_GROUPS][64];                                  /* per bin: RN(1 / |H|^2) in binary64 */
-    float stage[DEMOD_GROUPS][MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2]; /* one symbol's LLRs per group, deinterleaved; its first
-                                                                      576 bytes double as the FFT exchange area */
-    uint16_t smap[DEMOD_GROUPS][MIMO ? 2 * W_MAPLEN : W_MAPLEN];   /* the item's deinterleave table(s) */
+    float stage[DEMOD_GROUPS][(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2) + DEMOD_PAD]; /* one symbol's LLRs per group, deinterleaved; the
+                                                                      first 576 bytes double as the FFT exchange area */
+    float2 tw[8 * 9];                                              /* W64^(g*k1) at [g*9 + k1] */
+    uint16_t smap[DEMOD_GROUPS][(MIMO ? 2 : 1) * (W_MAPLEN + DEMOD_MAPPAD)]; /* the item's deinterleave table(s), each followed by pad entries */
 };
 
 template <bool MIMO> /* MIMO = false: one antenna, no two-stream code or registers at all */
@@ -166,8 +214,9 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     const int lane = tid & 31, g = tid & 7, base = lane & ~7, grp = tid >> 3;
     const int w = blockIdx.x * DEMOD_GROUPS + grp;
     const bool valid = w < nitems;
-    float wr[8], wi[8];
-    fft64_twiddles(g, wr, wi);
+    S.tw[(tid >> 3) * 9 + (tid & 7)] = make_float2(C8_W64_RE[((tid >> 3) * (tid & 7)) & 63], C8_W64_IM[((tid >> 3) * (tid & 7)) & 63]);
+    __syncthreads();
+    const float2* tw = S.tw;
 
     int p = 0, n0 = 0, nsy = 0;
     int fmt = 0, nss = 1, nb = 1, ncbps = 48, nsymsamp = 80;
@@ -228,12 +277,15 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
         const uint16_t* gm2 = T->map[14 + nbi];
         for (int k = g; k < nmap; k += 8) {
             smap[grp][k] = gm1[k];
-            if (MIMO) smap[grp][W_MAPLEN + k] = gm2[k];
+            if (MIMO) smap[grp][W_MAPLEN + DEMOD_MAPPAD + k] = gm2[k];
         }
+        /* bins without data: every bit of them goes to the row's pad slot */
+        smap[grp][W_MAPLEN + g] = (uint16_t)(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2);
+        if (MIMO) smap[grp][2 * W_MAPLEN + DEMOD_MAPPAD + g] = (uint16_t)DEMOD_STAGE;
         __syncwarp();
     }
     const uint16_t* map1 = smap[grp];
-    const uint16_t* map2 = smap[grp] + (MIMO ? W_MAPLEN : 0);
+    const uint16_t* map2 = smap[grp] + (MIMO ? W_MAPLEN + DEMOD_MAPPAD : 0);
     cf32 R[2][4];
 #pragma unroll
     for (int s2 = 0; s2 < 2; s2++)
@@ -258,8 +310,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
         if (any2) load_sym(src1 + (size_t)(it + 1) * nsymsamp, g, two && more, nx1);
 
         float re[8], im[8], re2[8], im2[8];
-        fft64_regs(cur0, g, myx, re, im, wr, wi);
-        if (any2) fft64_regs(cur1, g, myx, re2, im2, wr, wi);
+        fft64_regs(cur0, g, myx, re, im, tw);
+        if (any2) fft64_regs(cur1, g, myx, re2, im2, tw);
 
         cf32 e1[8], e2[8];
 #pragma unroll
@@ -269,9 +321,17 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             e2[k2] = c_make(0.f, 0.f);
             if (!MIMO || !two) {
                 /* every bin, used or not (unused bins divide by 1): no branch in the one-stream path */
+#if DEMOD_NOHOIST
+                /* keep the conversions of H and |H|^2 inside the loop: hoisted, they cost 48 registers */
+                asm volatile("" : "+f"(hh[k2].x), "+f"(hh[k2].y));
+#endif
                 const double hc = hh[k2].x, hd = hh[k2].y;
                 const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
+#if DEMOD_EQHOIST
+                e1[k2] = c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, eqr[grp][i]);
+#else
                 e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, eqr[grp][i]);
+#endif
             } else if (act && jj[k2] >= -1) {
                 {
                     const float4* H4 = reinterpret_cast<const float4*>(H + i * 4);
@@ -284,6 +344,10 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
                     e2[k2] = c_add(c_mul(t1, c_make(ia.z, ia.w)), c_mul(t2, c_make(ib.z, ib.w)));
                 }
             }
+        }
+        if (DEMOD_EQHOIST && (!MIMO || !two) && slow_div) {
+#pragma unroll
+            for (int k2 = 0; k2 < 8; k2++) e1[k2] = c_div(c_make(re[k2], im[k2]), hh[k2]);
         }
         /* the four pilots of each stream, to every lane of the group: bins 7, 21, 43, 57 */
         cf32 a7 = c_make(shfl_f(e1[0].x, base + 7), shfl_f(e1[0].y, base + 7));
@@ -340,10 +404,10 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
         }
         __syncwarp();
         if (act) {
-            /* the symbol's nCBPS floats leave as 16-byte vectors, 128 contiguous bytes per group and store */
-            float4* out4 = reinterpret_cast<float4*>(llr + llr_off + (size_t)n * ncbps);
-            const float4* s4 = reinterpret_cast<const float4*>(stg);
-            for (int k = g; k < (ncbps >> 2); k += 8) out4[k] = s4[k];
+            /* the symbol's nCBPS floats leave as 8-byte vectors (rows are 8-byte aligned), 64 contiguous bytes per group and store */
+            float2* out2 = reinterpret_cast<float2*>(llr + llr_off + (size_t)n * ncbps);
+            const float2* s2 = reinterpret_cast<const float2*>(stg);
+            for (int k = g; k < (ncbps >> 1); k += 8) out2[k] = s2[k];
         }
         __syncwarp();
 #pragma unroll

@@ -6,9 +6,10 @@
  *  - descramble: the 7-bit scrambler state is read from the first 7 decoded bits; the x^7+x^4+1
  *    sequence is generated once per packet (160 bits) and applied 32 bits at a time;
  *  - bytes: LSB first from bit 16, i.e. the descrambled bit words viewed as bytes, offset 2;
- *  - CRC-32 (reflected 0xEDB88320, init/xorout 0xFFFFFFFF): every lane runs a table CRC over its
- *    own slice of the MPDU, the 32 partial CRCs are merged with x^(8n) multiplications in
- *    GF(2)[x]/P, and the result is compared with the residue 558161692 the reference tests for;
+ *  - CRC-32 (reflected 0xEDB88320, init/xorout 0xFFFFFFFF): every lane runs a four-bytes-per-step table CRC
+ *    (tables made on the host, tables.cc) over its own slice of the MPDU, the 32 partial CRCs are merged with
+ *    x^(8n) multiplications in GF(2)[x]/P, and the result is compared with the residue 558161692 the reference
+ *    tests for;
  *  - VHT: the delimiter walk of the reference, with its quirks (no delimiter CRC/signature check,
  *    length bits OR-ed into a value that survives from the previous subframe, +4 after a pass).
  */
@@ -20,7 +21,7 @@
 #define CRC_RESIDUE 558161692u
 
 struct PostSmem {
-    uint32_t crc_tab[256];
+    uint32_t crc_tab[4][256];
     uint32_t x2n[32]; /* x^(2^k) mod P, reflected */
     uint32_t dw[POST_WARPS][POST_MAXW];
     uint32_t seq[POST_WARPS][8];
@@ -51,8 +52,9 @@ __device__ __forceinline__ uint32_t x_pow_bytes(const uint32_t* x2n, uint32_t nb
     return p;
 }
 
-/* standard CRC-32 of by[0..n), computed by the whole warp; every lane gets the result */
-__device__ uint32_t warp_crc32(const PostSmem& S, const uint8_t* by, int n, int lane)
+/* standard CRC-32 of the n bytes that start at byte 2 of dw[woff] (PSDU bytes sit at bit offset 16 of the descrambled
+ * words; A-MPDU subframes start on 4-byte boundaries), computed by the whole warp; every lane gets the result */
+__device__ uint32_t warp_crc32(const PostSmem& S, const uint32_t* __restrict__ xpow8, const uint32_t* dw, int woff, int n, int lane)
 {
     if (n <= 0) return 0u;
     int c = (n + 31) >> 5;
@@ -62,10 +64,20 @@ __device__ uint32_t warp_crc32(const PostSmem& S, const uint8_t* by, int n, int 
     uint32_t crc = 0u;
     if (beg < end) {
         crc = 0xFFFFFFFFu;
-        for (int k = beg; k < end; k++) crc = S.crc_tab[(crc ^ by[k]) & 0xffu] ^ (crc >> 8);
+        const uint32_t* w = dw + woff + (beg >> 2);
+        uint32_t lo = w[0];
+        int k = beg;
+        for (; k + 4 <= end; k += 4) {
+            const uint32_t hi = *++w;
+            const uint32_t x = crc ^ __funnelshift_r(lo, hi, 16);
+            lo = hi;
+            crc = S.crc_tab[3][x & 0xffu] ^ S.crc_tab[2][(x >> 8) & 0xffu] ^ S.crc_tab[1][(x >> 16) & 0xffu] ^ S.crc_tab[0][x >> 24];
+        }
+        const uint8_t* by = reinterpret_cast<const uint8_t*>(dw + woff) + 2;
+        for (; k < end; k++) crc = S.crc_tab[0][(crc ^ by[k]) & 0xffu] ^ (crc >> 8);
         crc ^= 0xFFFFFFFFu;
         int after = n - end;
-        if (after > 0) crc = gf_mul(x_pow_bytes(S.x2n, (uint32_t)after), crc);
+        if (after > 0) crc = gf_mul(after < W_XPOW8 ? __ldg(&xpow8[after]) : x_pow_bytes(S.x2n, (uint32_t)after), crc);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) crc ^= __shfl_xor_sync(0xffffffffu, crc, o);
@@ -93,7 +105,7 @@ __device__ __forceinline__ void emit(int lane, uint32_t pkt, uint32_t off, uint3
 }
 
 /* counters: [0] MPDU records, [1] FCS-valid MPDUs, [2..3] 64-bit sum of 8*len over FCS-valid MPDUs */
-__global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(int ndec, const int4* __restrict__ grp, const int* __restrict__ pkt_slot,
+__global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(const W80211Tables* __restrict__ tab, int ndec, const int4* __restrict__ grp, const int* __restrict__ pkt_slot,
                                                                const int* __restrict__ dec_list, const w80211_desc* __restrict__ desc,
                                                                const uint32_t* __restrict__ bits, const uint32_t* __restrict__ psdu_off,
                                                                uint8_t* __restrict__ out_bytes, w80211_mpdu* __restrict__ mpdus,
@@ -101,19 +113,8 @@ __global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(int ndec, const i
 {
     __shared__ PostSmem S;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    for (int i = tid; i < 256; i += blockDim.x) {
-        uint32_t c = (uint32_t)i;
-        for (int k = 0; k < 8; k++) c = (c & 1u) ? (CRC_POLY ^ (c >> 1)) : (c >> 1);
-        S.crc_tab[i] = c;
-    }
-    if (tid == 0) {
-        uint32_t p = 0x40000000u; /* x^1 */
-        S.x2n[0] = p;
-        for (int k = 1; k < 32; k++) {
-            p = gf_mul(p, p);
-            S.x2n[k] = p;
-        }
-    }
+    for (int i = tid; i < 1024; i += blockDim.x) (&S.crc_tab[0][0])[i] = __ldg(&tab->crc_tab[0][0] + i);
+    if (tid < 32) S.x2n[tid] = __ldg(&tab->crc_x2n[tid]);
     __syncthreads();
     const int q = blockIdx.x * POST_WARPS + wid;
     if (q >= ndec) return;
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(int ndec, const i
 
     if (d.format != W80211_F_VHT) {
         if (d.ampdu) return; /* HT A-MPDU: the reference publishes nothing (decode_impl.cc:432-435) */
-        uint32_t crc = warp_crc32(S, by, nbytes, lane);
+        uint32_t crc = warp_crc32(S, tab->crc_xpow8, dw, 0, nbytes, lane);
         emit(lane, (uint32_t)pkt, poff, (uint32_t)nbytes, nbytes == d.len && crc == CRC_RESIDUE, mpdus, mpdu_cap, counters);
         return;
     }
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(int ndec, const i
         procd += padded * 8;
         if (procd > T) break;
         pos += 4;
-        uint32_t crc = warp_crc32(S, by + pos, tmplen, lane);
+        uint32_t crc = warp_crc32(S, tab->crc_xpow8, dw, pos >> 2, tmplen, lane);
         bool ok = crc == CRC_RESIDUE;
         emit(lane, (uint32_t)pkt, poff + (uint32_t)pos, (uint32_t)tmplen, ok, mpdus, mpdu_cap, counters);
         pos += padded;
@@ -201,12 +202,12 @@ __global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(int ndec, const i
     }
 }
 
-void w_launch_post(cudaStream_t st, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,
+void w_launch_post(cudaStream_t st, const W80211Tables* tab, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,
                    const w80211_desc* desc, const uint32_t* bits, const uint32_t* psdu_off, uint8_t* out_bytes,
                    w80211_mpdu* mpdus, unsigned int mpdu_cap, unsigned int* counters)
 {
     if (npkt_dec <= 0) return;
     int blocks = (npkt_dec + POST_WARPS - 1) / POST_WARPS;
-    post_kernel<<<blocks, POST_WARPS * 32, 0, st>>>(npkt_dec, grp, pkt_slot, dec_list, desc, bits, psdu_off, out_bytes, mpdus,
+    post_kernel<<<blocks, POST_WARPS * 32, 0, st>>>(tab, npkt_dec, grp, pkt_slot, dec_list, desc, bits, psdu_off, out_bytes, mpdus,
                                                     mpdu_cap, counters);
 }

@@ -22,9 +22,32 @@ static int interleave_pos(int k, int ncbpss, int nbpscs, bool legacy, int iss)
     return j;
 }
 
+/* a(x) * b(x) mod P in the reflected bit order of CRC-32 (bit 31 = x^0) */
+static uint32_t crc_gf_mul(uint32_t a, uint32_t b)
+{
+    uint32_t p = 0;
+    for (int i = 31; i >= 0; i--) {
+        if ((a >> i) & 1u) p ^= b;
+        b = (b & 1u) ? (b >> 1) ^ 0xEDB88320u : (b >> 1);
+    }
+    return p;
+}
+
 void w80211_fill_tables(W80211Tables* t)
 {
     memset(t, 0, sizeof(*t));
+    /* CRC-32: byte table, three more tables for four bytes per step, and x^(2^k) mod P for joining partial CRCs */
+    for (int i = 0; i < 256; i++) {
+        uint32_t c = (uint32_t)i;
+        for (int k = 0; k < 8; k++) c = (c & 1u) ? (0xEDB88320u ^ (c >> 1)) : (c >> 1);
+        t->crc_tab[0][i] = c;
+    }
+    for (int s = 1; s < 4; s++)
+        for (int i = 0; i < 256; i++) t->crc_tab[s][i] = (t->crc_tab[s - 1][i] >> 8) ^ t->crc_tab[0][t->crc_tab[s - 1][i] & 0xffu];
+    t->crc_x2n[0] = 0x40000000u; /* x^1 */
+    for (int k = 1; k < 32; k++) t->crc_x2n[k] = crc_gf_mul(t->crc_x2n[k - 1], t->crc_x2n[k - 1]);
+    t->crc_xpow8[0] = 0x80000000u; /* x^0 */
+    for (int n = 1; n < W_XPOW8; n++) t->crc_xpow8[n] = crc_gf_mul(t->crc_x2n[3], t->crc_xpow8[n - 1]);
     /* pilot polarity: scrambler output with the all-ones seed, 0 -> +1, 1 -> -1 (17.3.5.10) */
     int st = 0x7f;
     for (int i = 0; i < 127; i++) {

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 TAB_DTYPE = np.dtype([("pilot_p", "<f4", 128), ("ltf_nl", "<f4", 64), ("sig_demap", "i1", 64), ("bin_j_l", "i1", 64),
                       ("bin_j_nl", "i1", 64), ("sigb_deint", "u1", 52), ("sigb_int", "u1", 52),
-                      ("map", "<u2", (19, 416))], align=True)
+                      ("map", "<u2", (19, 416)), ("crc_tab", "<u4", (4, 256)), ("crc_x2n", "<u4", 32), ("crc_xpow8", "<u4", 4224)], align=True)
 
 
 @pytest.fixture(scope="module")
@@ -26,6 +26,58 @@ def tab():
     L.w80211_fill_tables.restype = None
     L.w80211_fill_tables(t.ctypes.data)
     return t[0]
+
+
+def _gf_mul(a, b):
+    p = 0
+    for i in range(31, -1, -1):
+        if (a >> i) & 1:
+            p ^= b
+        b = (b >> 1) ^ 0xEDB88320 if b & 1 else b >> 1
+    return p
+
+
+def test_crc_tables_against_zlib(tab):
+    """post.cu's CRC-32 tables (boost::crc_32_type of decode_impl.h:84 is the zlib CRC): four bytes per step through
+    crc_tab, partial CRCs joined with x^(8n) from crc_x2n, exactly as warp_crc32 does."""
+    import zlib
+    T = [[int(v) for v in tab["crc_tab"][s]] for s in range(4)]
+    x2n = [int(v) for v in tab["crc_x2n"]]
+
+    def crc_words(data):
+        crc = 0xFFFFFFFF
+        k = 0
+        while k + 4 <= len(data):
+            x = crc ^ int.from_bytes(data[k:k + 4], "little")
+            crc = T[3][x & 255] ^ T[2][(x >> 8) & 255] ^ T[1][(x >> 16) & 255] ^ T[0][x >> 24]
+            k += 4
+        for b in data[k:]:
+            crc = T[0][(crc ^ b) & 255] ^ (crc >> 8)
+        return crc ^ 0xFFFFFFFF
+
+    def x_pow_bytes(n):
+        p, k = 0x80000000, 3
+        while n:
+            if n & 1:
+                p = _gf_mul(x2n[k & 31], p)
+            n >>= 1
+            k += 1
+        return p
+
+    for n in (0, 1, 2, 7, 100, 1333, 4095, 4223):
+        assert int(tab["crc_xpow8"][n]) == x_pow_bytes(n)
+    rng = np.random.default_rng(5)
+    for n in (1, 3, 4, 5, 94, 1500, 4095):
+        data = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        assert crc_words(data) == zlib.crc32(data)
+        cut = n // 3
+        a, b = data[:cut], data[cut:]
+        joined = (_gf_mul(x_pow_bytes(len(b)), crc_words(a)) if a else 0) ^ crc_words(b)
+        assert joined == zlib.crc32(data)
+    # the residue the reference tests for (decode_impl.cc:374,453): CRC over data + FCS
+    frame = rng.integers(0, 256, 90, dtype=np.uint8).tobytes()
+    frame += zlib.crc32(frame).to_bytes(4, "little")
+    assert crc_words(frame) == 558161692
 
 
 def test_library_exports_every_declared_symbol():
