@@ -41,10 +41,13 @@ struct PinBuf {
     size_t cap = 0;
 };
 
-enum { EV_START, EV_H2D, EV_HDR, EV_PLAN, EV_DEMOD, EV_VIT, EV_TB, EV_POST, EV_END, EV_COUNT };
+enum { EV_START, EV_H2D, EV_HDR0, EV_HDR, EV_PLAN, EV_DEMOD, EV_VIT0, EV_VIT, EV_TB, EV_POST, EV_END, EV_COUNT };
 
 struct Slot {
     cudaStream_t stream = nullptr;
+    /* The header kernel runs on a high-priority stream of its own: the host needs its descriptors to plan the batch, so
+     * its blocks go first whenever the other slot's Viterbi blocks retire, and the host plans while that kernel runs on. */
+    cudaStream_t hstream = nullptr;
     cudaEvent_t ev[EV_COUNT] = {};
     bool busy = false;
     /* device */
@@ -61,6 +64,9 @@ struct Slot {
     uint32_t launches = 0;
     w80211_batch_out* out = nullptr;
     std::vector<uint32_t> h_psdu_off;
+    /* host plan scratch, kept between batches (a fresh 0.5 MB vector per array and batch costs page faults) */
+    std::vector<int> v_symprefix, v_dec, v_slot_pkt, v_pkt_slot;
+    std::vector<int4> v_grp;
     w80211_timing timing = {};
     float host_plan_ms = 0.f;
 };
@@ -81,6 +87,7 @@ struct SigStage {
 struct w80211_ctx {
     int device = 0;
     int nslots = 2;
+    cudaEvent_t last_tail = nullptr; /* EV_POST of the batch whose decode tail was enqueued last (see enqueue_decode_tail) */
     W80211Tables* d_tab = nullptr;
     Slot slots[4];
     SigStage sig;
@@ -169,7 +176,8 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     const int npkt = s.npkt;
     /* LLR layout and symbol prefix sums */
     uint64_t off = 0;
-    std::vector<int> symprefix(npkt + 1, 0);
+    std::vector<int>& symprefix = s.v_symprefix;
+    symprefix.assign((size_t)npkt + 1, 0);
     for (int p = 0; p < npkt; p++) {
         w80211_desc& d = hd[p];
         int nsym = 0;
@@ -188,7 +196,8 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     s.nsymtot = symprefix[npkt];
 
     /* packets to decode, sorted by (code rate, trellis descending) */
-    std::vector<int> dec;
+    std::vector<int>& dec = s.v_dec;
+    dec.clear();
     s.trellis_steps = 0;
     if (do_decode) {
         for (int p = 0; p < npkt; p++) {
@@ -208,8 +217,11 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
         if (!std::is_sorted(dec.begin(), dec.end(), before)) std::stable_sort(dec.begin(), dec.end(), before); /* homogeneous batches: nothing to do */
     }
     s.ndec = (int)dec.size();
-    std::vector<int> slot_pkt, pkt_slot(npkt, -1);
-    std::vector<int4> grp;
+    std::vector<int>&slot_pkt = s.v_slot_pkt, &pkt_slot = s.v_pkt_slot;
+    std::vector<int4>& grp = s.v_grp;
+    slot_pkt.clear();
+    grp.clear();
+    pkt_slot.assign((size_t)npkt, -1);
     s.h_psdu_off.assign(npkt, 0);
     uint64_t row = 0, wrow = 0, boff = 0;
     for (int c = 0; c <= 4; c++) s.cr_first[c] = 0;
@@ -287,6 +299,12 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
 {
     cudaStream_t st = s.stream;
     w80211_batch_out* out = s.out;
+    /* Several batches in flight: this batch's Viterbi kernel starts only after the previous batch's traceback and post
+     * kernels.  Two Viterbi kernels never interleave their waves and a tail never shares the SMs with the next Viterbi
+     * kernel, so the slots alternate (one in its Viterbi kernel, the other in tail -> host collect/plan -> header ->
+     * demod) instead of falling into lockstep with the GPU idle while the host collects and plans. */
+    if (ctx->last_tail && ctx->last_tail != s.ev[EV_POST]) CK(cudaStreamWaitEvent(st, ctx->last_tail, 0));
+    CK(cudaEventRecord(s.ev[EV_VIT0], st));
     int nvit = w_launch_viterbi(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
                                 (const float*)s.llr.p, (uint2*)s.surv.p);
     CK(cudaGetLastError());
@@ -307,6 +325,7 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
                   (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_POST], st));
+    ctx->last_tail = s.ev[EV_POST];
     if (s.ngroups > 0) s.launches += 2 + nvit;
     /* results */
     CK(cudaMemcpyAsync(s.h_counters.p, s.counters.p, 64, cudaMemcpyDeviceToHost, st));
@@ -422,13 +441,16 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
     RS(dev_reserve(ctx, s.desc, (size_t)npkt * sizeof(w80211_desc) + 16));
     RS(dev_reserve(ctx, s.chan, (size_t)npkt * chan_stride * 8 + 16));
     RS(pin_reserve(ctx, s.h_desc, (size_t)npkt * sizeof(w80211_desc) + 16));
-    w_launch_header(st, ctx->d_tab, npkt, in->nant, d_iq[0], d_iq[1], in->nsamples, d_pk, d_chin, (w80211_desc*)s.desc.p,
+    cudaStream_t hs = s.hstream ? s.hstream : st;
+    if (hs != st) CK(cudaStreamWaitEvent(hs, s.ev[EV_H2D], 0));
+    CK(cudaEventRecord(s.ev[EV_HDR0], hs));
+    w_launch_header(hs, ctx->d_tab, npkt, in->nant, d_iq[0], d_iq[1], in->nsamples, d_pk, d_chin, (w80211_desc*)s.desc.p,
                     (float2*)s.chan.p, chan_stride, in->mu_pos ? 1 : 0);
     CK(cudaGetLastError());
     if (npkt) s.launches += 1;
-    CK(cudaEventRecord(s.ev[EV_HDR], st));
-    if (npkt) CK(cudaMemcpyAsync(s.h_desc.p, s.desc.p, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    CK(cudaEventRecord(s.ev[EV_HDR], hs));
+    if (npkt) CK(cudaMemcpyAsync(s.h_desc.p, s.desc.p, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost, hs));
+    CK(cudaStreamSynchronize(hs)); /* everything enqueued on st from here on comes after the header stage */
     w80211_desc* hd = (w80211_desc*)s.h_desc.p;
     const auto tp0 = std::chrono::steady_clock::now();
     RS(plan_and_upload(ctx, s, hd, true, do_decode));
@@ -525,11 +547,11 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
     memset(&t, 0, sizeof(t));
     if (s.did_demod) {
         t.h2d = ms(EV_START, EV_H2D);
-        t.header = ms(EV_H2D, EV_HDR);
+        t.header = ms(EV_HDR0, EV_HDR);
         t.demod = ms(EV_PLAN, EV_DEMOD);
     }
     if (s.did_decode) {
-        t.viterbi = ms(s.did_demod ? EV_DEMOD : EV_PLAN, EV_VIT);
+        t.viterbi = ms(EV_VIT0, EV_VIT);
         t.traceback = ms(EV_VIT, EV_TB);
         t.post = ms(EV_TB, EV_POST);
         t.d2h = ms(EV_POST, EV_END);
@@ -591,8 +613,11 @@ int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
     bool ok = cudaMalloc(&ctx->d_tab, sizeof(W80211Tables)) == cudaSuccess &&
               cudaMemcpy(ctx->d_tab, ht, sizeof(W80211Tables), cudaMemcpyHostToDevice) == cudaSuccess;
     delete ht;
+    int prio_lo = 0, prio_hi = 0;
+    ok = ok && cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) == cudaSuccess;
     for (int i = 0; ok && i < ctx->nslots; i++) {
-        ok = cudaStreamCreateWithFlags(&ctx->slots[i].stream, cudaStreamNonBlocking) == cudaSuccess;
+        ok = cudaStreamCreateWithPriority(&ctx->slots[i].stream, cudaStreamNonBlocking, prio_lo) == cudaSuccess &&
+             cudaStreamCreateWithPriority(&ctx->slots[i].hstream, cudaStreamNonBlocking, prio_hi) == cudaSuccess;
         for (int e = 0; ok && e < EV_COUNT; e++) ok = cudaEventCreate(&ctx->slots[i].ev[e]) == cudaSuccess;
     }
     if (!ok) {
@@ -621,6 +646,7 @@ void w80211_destroy(w80211_ctx* ctx)
         for (int e = 0; e < EV_COUNT; e++)
             if (s.ev[e]) cudaEventDestroy(s.ev[e]);
         if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.hstream) cudaStreamDestroy(s.hstream);
     }
     {
         SigStage& g = ctx->sig;
