@@ -45,9 +45,6 @@ enum { EV_START, EV_H2D, EV_HDR0, EV_HDR, EV_PLAN, EV_DEMOD, EV_VIT0, EV_VIT, EV
 
 struct Slot {
     cudaStream_t stream = nullptr;
-    /* The header kernel runs on a high-priority stream of its own: the host needs its descriptors to plan the batch, so
-     * its blocks go first whenever the other slot's Viterbi blocks retire, and the host plans while that kernel runs on. */
-    cudaStream_t hstream = nullptr;
     cudaEvent_t ev[EV_COUNT] = {};
     bool busy = false;
     /* device */
@@ -58,6 +55,7 @@ struct Slot {
     /* batch in flight */
     int npkt = 0, nant = 1, ngroups = 0, ndec = 0, nsymtot = 0;
     int cr_first[5] = {0, 0, 0, 0, 0};
+    size_t plan_o_psdu = 0; /* offset of the psdu_off array inside h_plan */
     bool did_demod = false, did_decode = false, in_host = true;
     uint64_t n_llr = 0, n_bytes = 0, trellis_steps = 0;
     uint32_t mpdu_cap = 0;
@@ -87,7 +85,8 @@ struct SigStage {
 struct w80211_ctx {
     int device = 0;
     int nslots = 2;
-    cudaEvent_t last_tail = nullptr; /* EV_POST of the batch whose decode tail was enqueued last (see enqueue_decode_tail) */
+    cudaEvent_t origin = nullptr;    /* W80211_TRACE=1: time zero of the per-batch timelines printed by collect_slot */
+    cudaEvent_t last_tail = nullptr; /* EV_POST of the batch whose decode was enqueued last (see enqueue_front) */
     W80211Tables* d_tab = nullptr;
     Slot slots[4];
     SigStage sig;
@@ -280,6 +279,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     if (sz_g) memcpy(hp + o_g, grp.data(), sz_g);
     if (sz_d) memcpy(hp + o_d, dec.data(), sz_d);
     memcpy(hp + o_po, s.h_psdu_off.data(), sz_po);
+    s.plan_o_psdu = o_po;
     cudaStream_t st = s.stream;
     CK(cudaMemcpyAsync(s.symprefix.p, hp + o_sym, sz_sym, cudaMemcpyHostToDevice, st));
     if (do_decode) {
@@ -299,11 +299,6 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
 {
     cudaStream_t st = s.stream;
     w80211_batch_out* out = s.out;
-    /* Several batches in flight: this batch's Viterbi kernel starts only after the previous batch's traceback and post
-     * kernels.  Two Viterbi kernels never interleave their waves and a tail never shares the SMs with the next Viterbi
-     * kernel, so the slots alternate (one in its Viterbi kernel, the other in tail -> host collect/plan -> header ->
-     * demod) instead of falling into lockstep with the GPU idle while the host collects and plans. */
-    if (ctx->last_tail && ctx->last_tail != s.ev[EV_POST]) CK(cudaStreamWaitEvent(st, ctx->last_tail, 0));
     CK(cudaEventRecord(s.ev[EV_VIT0], st));
     int nvit = w_launch_viterbi(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
                                 (const float*)s.llr.p, (uint2*)s.surv.p);
@@ -320,9 +315,16 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
     RS(pin_reserve(ctx, s.h_mpdus, (size_t)internal_cap * sizeof(w80211_mpdu)));
     RS(pin_reserve(ctx, s.h_counters, 64));
     s.mpdu_cap = internal_cap;
+    /* Results for a caller with device buffers are written in place (PSDU bytes by the post kernel) or uploaded from the
+     * pinned host copies (descriptors, offsets): no device-to-device copy kernel, which would have to wait for SMs while
+     * another slot's Viterbi kernel holds all of them and so delay rx_collect by half that kernel's duration. */
+    const bool bytes_in_place = out->bytes && out->mem == W80211_MEM_DEVICE && ((uintptr_t)out->bytes & 15u) == 0;
+    if (out->bytes && out->bytes_capacity < s.n_bytes)
+        return fail(ctx, W80211_E_CAPACITY, "bytes_capacity %llu < %llu needed", (unsigned long long)out->bytes_capacity,
+                    (unsigned long long)s.n_bytes);
     w_launch_post(st, ctx->d_tab, s.ndec, (const int4*)s.grp.p, (const int*)s.pkt_slot.p, (const int*)s.dec_list.p,
-                  (const w80211_desc*)s.desc.p, (const uint32_t*)s.bits.p, (const uint32_t*)s.psdu_off.p, (uint8_t*)s.bytes.p,
-                  (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
+                  (const w80211_desc*)s.desc.p, (const uint32_t*)s.bits.p, (const uint32_t*)s.psdu_off.p,
+                  bytes_in_place ? out->bytes : (uint8_t*)s.bytes.p, (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_POST], st));
     ctx->last_tail = s.ev[EV_POST];
@@ -330,16 +332,12 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
     /* results */
     CK(cudaMemcpyAsync(s.h_counters.p, s.counters.p, 64, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(s.h_mpdus.p, s.mpdus.p, (size_t)internal_cap * sizeof(w80211_mpdu), cudaMemcpyDeviceToHost, st));
-    if (out->bytes) {
-        if (out->bytes_capacity < s.n_bytes) return fail(ctx, W80211_E_CAPACITY, "bytes_capacity %llu < %llu needed",
-                                                         (unsigned long long)out->bytes_capacity, (unsigned long long)s.n_bytes);
-        if (s.n_bytes)
-            CK(cudaMemcpyAsync(out->bytes, s.bytes.p, s.n_bytes,
-                               out->mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
-    }
+    if (out->bytes && !bytes_in_place && s.n_bytes)
+        CK(cudaMemcpyAsync(out->bytes, s.bytes.p, s.n_bytes,
+                           out->mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
     if (out->psdu_off) {
         if (out->mem == W80211_MEM_DEVICE)
-            CK(cudaMemcpyAsync(out->psdu_off, s.psdu_off.p, (size_t)s.npkt * 4, cudaMemcpyDeviceToDevice, st));
+            CK(cudaMemcpyAsync(out->psdu_off, (const char*)s.h_plan.p + s.plan_o_psdu, (size_t)s.npkt * 4, cudaMemcpyHostToDevice, st));
         else
             memcpy(out->psdu_off, s.h_psdu_off.data(), (size_t)s.npkt * 4);
     }
@@ -353,7 +351,7 @@ int finish_outputs(w80211_ctx* ctx, Slot& s)
     const w80211_desc* hd = (const w80211_desc*)s.h_desc.p;
     if (out->desc) {
         if (out->mem == W80211_MEM_DEVICE)
-            CK(cudaMemcpyAsync(out->desc, s.desc.p, (size_t)s.npkt * sizeof(w80211_desc), cudaMemcpyDeviceToDevice, st));
+            CK(cudaMemcpyAsync(out->desc, hd, (size_t)s.npkt * sizeof(w80211_desc), cudaMemcpyHostToDevice, st));
         else
             memcpy(out->desc, hd, (size_t)s.npkt * sizeof(w80211_desc));
     }
@@ -441,20 +439,27 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
     RS(dev_reserve(ctx, s.desc, (size_t)npkt * sizeof(w80211_desc) + 16));
     RS(dev_reserve(ctx, s.chan, (size_t)npkt * chan_stride * 8 + 16));
     RS(pin_reserve(ctx, s.h_desc, (size_t)npkt * sizeof(w80211_desc) + 16));
-    cudaStream_t hs = s.hstream ? s.hstream : st;
-    if (hs != st) CK(cudaStreamWaitEvent(hs, s.ev[EV_H2D], 0));
-    CK(cudaEventRecord(s.ev[EV_HDR0], hs));
-    w_launch_header(hs, ctx->d_tab, npkt, in->nant, d_iq[0], d_iq[1], in->nsamples, d_pk, d_chin, (w80211_desc*)s.desc.p,
+    CK(cudaEventRecord(s.ev[EV_HDR0], st));
+    w_launch_header(st, ctx->d_tab, npkt, in->nant, d_iq[0], d_iq[1], in->nsamples, d_pk, d_chin, (w80211_desc*)s.desc.p,
                     (float2*)s.chan.p, chan_stride, in->mu_pos ? 1 : 0);
     CK(cudaGetLastError());
     if (npkt) s.launches += 1;
-    CK(cudaEventRecord(s.ev[EV_HDR], hs));
-    if (npkt) CK(cudaMemcpyAsync(s.h_desc.p, s.desc.p, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost, hs));
-    CK(cudaStreamSynchronize(hs)); /* everything enqueued on st from here on comes after the header stage */
+    CK(cudaEventRecord(s.ev[EV_HDR], st));
+    if (npkt) CK(cudaMemcpyAsync(s.h_desc.p, s.desc.p, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     w80211_desc* hd = (w80211_desc*)s.h_desc.p;
     const auto tp0 = std::chrono::steady_clock::now();
     RS(plan_and_upload(ctx, s, hd, true, do_decode));
     s.host_plan_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tp0).count();
+    /* Several batches in flight: this batch's demod kernel (and with it its Viterbi kernel) waits for the traceback and
+     * post kernels of the batch enqueued before it, i.e. for that batch's whole decode.  The GPU then runs
+     *     Viterbi A | traceback A, post A | demod B | Viterbi B | traceback B, post B | demod A' | ...
+     * one big kernel at a time -- sharing the SMs with a Viterbi kernel slows both sides down by more than running
+     * them in turn (it uses 84 % of the issue slots; profiles/experiments/r1_overlap_shared_viterbi_stream.txt) -- and
+     * the slots alternate instead of falling into lockstep (both Viterbi kernels interleaved, both tails at once, then
+     * an idle GPU while the host collects and plans): the header kernel, the host plan and rx_collect of one slot all
+     * happen while the other slot's Viterbi kernel runs. */
+    if (ctx->last_tail && ctx->last_tail != s.ev[EV_POST]) CK(cudaStreamWaitEvent(st, ctx->last_tail, 0));
     CK(cudaEventRecord(s.ev[EV_PLAN], st));
     w_launch_demod(st, ctx->d_tab, s.nsymtot, npkt, in->nant, d_iq[0], d_iq[1], d_pk, (const w80211_desc*)s.desc.p,
                    (const int*)s.symprefix.p, (const float2*)s.chan.p, chan_stride, (float*)s.llr.p);
@@ -557,6 +562,18 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
         t.d2h = ms(EV_POST, EV_END);
     }
     t.total = ms(EV_START, EV_END);
+    if (ctx->origin && s.did_demod && s.did_decode) {
+        /* diagnostics: when each stage of this batch ended on the device, in ms since the context was created */
+        static const int evs[] = {EV_START, EV_HDR0, EV_HDR, EV_PLAN, EV_DEMOD, EV_VIT0, EV_VIT, EV_TB, EV_POST, EV_END};
+        static const char* names[] = {"start", "hdr0", "hdr", "plan", "demod", "vit0", "vit", "tb", "post", "end"};
+        fprintf(stderr, "w80211 timeline slot %d:", (int)(&s - ctx->slots));
+        for (int i = 0; i < 10; i++) {
+            float v = 0.f;
+            cudaEventElapsedTime(&v, ctx->origin, s.ev[evs[i]]);
+            fprintf(stderr, " %s %.2f", names[i], v);
+        }
+        fprintf(stderr, "\n");
+    }
     t.launches = s.launches;
     t.host_plan = s.host_plan_ms;
     t.host_collect = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tc0).count();
@@ -613,13 +630,11 @@ int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
     bool ok = cudaMalloc(&ctx->d_tab, sizeof(W80211Tables)) == cudaSuccess &&
               cudaMemcpy(ctx->d_tab, ht, sizeof(W80211Tables), cudaMemcpyHostToDevice) == cudaSuccess;
     delete ht;
-    int prio_lo = 0, prio_hi = 0;
-    ok = ok && cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) == cudaSuccess;
     for (int i = 0; ok && i < ctx->nslots; i++) {
-        ok = cudaStreamCreateWithPriority(&ctx->slots[i].stream, cudaStreamNonBlocking, prio_lo) == cudaSuccess &&
-             cudaStreamCreateWithPriority(&ctx->slots[i].hstream, cudaStreamNonBlocking, prio_hi) == cudaSuccess;
+        ok = cudaStreamCreateWithFlags(&ctx->slots[i].stream, cudaStreamNonBlocking) == cudaSuccess;
         for (int e = 0; ok && e < EV_COUNT; e++) ok = cudaEventCreate(&ctx->slots[i].ev[e]) == cudaSuccess;
     }
+    if (ok && getenv("W80211_TRACE")) ok = cudaEventCreate(&ctx->origin) == cudaSuccess && cudaEventRecord(ctx->origin, 0) == cudaSuccess;
     if (!ok) {
         cudaGetLastError();
         w80211_destroy(ctx);
@@ -646,7 +661,6 @@ void w80211_destroy(w80211_ctx* ctx)
         for (int e = 0; e < EV_COUNT; e++)
             if (s.ev[e]) cudaEventDestroy(s.ev[e]);
         if (s.stream) cudaStreamDestroy(s.stream);
-        if (s.hstream) cudaStreamDestroy(s.hstream);
     }
     {
         SigStage& g = ctx->sig;
@@ -663,6 +677,7 @@ void w80211_destroy(w80211_ctx* ctx)
             if (e) cudaEventDestroy(e);
         if (g.stream) cudaStreamDestroy(g.stream);
     }
+    if (ctx->origin) cudaEventDestroy(ctx->origin);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
     delete ctx;
 }
