@@ -502,7 +502,12 @@ def main_gpu(args):
     sm_clk = clk["sm_mhz"] or float(peaks.get("sm_max_mhz", 1965.0))
     acs_per_s = steps_per_launch * 64 / (vit_ms * 1e-3)
     acs_peak = nsm * 128 * sm_clk * 1e6 / 3.0
-    alu_peak = nsm * 4 * 32 * sm_clk * 1e6 / 4.0  # per ACS: FMNMX + SHF on the ALU pipe, 2 cycles each per warp and SMSP (profiles/r1_pipebench.txt)
+    # per ACS the rate-3/4 body issues 1633 / 384 = 4.25 warp-instructions (834 FADD, 384 FMNMX, 384 SHF per six steps and
+    # 64 states, cuobjdump -sass); one scheduler issues one warp-instruction per clock, so instruction issue bounds the kernel
+    # before any pipe does (profiles/r1_pipebench.txt: FMNMX 1 and SHF 2 cycles of the ALU pipe per warp, FADD on the FMA pipe)
+    INSTR_PER_ACS = 1633.0 / 384.0
+    issue_peak = nsm * 4 * 32 * sm_clk * 1e6 / INSTR_PER_ACS
+    alu_peak = nsm * 4 * 32 * sm_clk * 1e6 / 3.0
     demod_ms = stage["demod"] / KSEQ
     demod_bytes = float(P) * nsym * (nsymsamp * 8 + ncbps * 4)
     tb_ms = stage["traceback"] / KSEQ
@@ -536,8 +541,10 @@ def main_gpu(args):
         "roofline_compute": {"kernel": "viterbi_kernel", "bound": "fp32+alu issue", "achieved": acs_per_s / 1e12, "peak": acs_peak / 1e12,
                              "unit": "T ACS/s", "frac": acs_per_s / acs_peak,
                              "peak_def": "SMs x 128 lanes x SM clock under load / 3 lane-ops per ACS (SURVEY.md 8(d))", "sm_mhz": sm_clk,
+                             "issue_peak": issue_peak / 1e12, "issue_frac": acs_per_s / issue_peak,
+                             "issue_def": "SMs x 4 schedulers x 32 lanes x clock / 4.25 warp-instructions per ACS (1633 per 6-step body of 384 ACS: 834 FADD, 384 FMNMX, 384 SHF)",
                              "alu_pipe_peak": alu_peak / 1e12, "alu_pipe_frac": acs_per_s / alu_peak,
-                             "alu_pipe_def": "per ACS one FMNMX and one SHF, both on the half-rate ALU pipe: SMs x 4 SMSPs x 32 lanes x clock / 4 cycles"},
+                             "alu_pipe_def": "per ACS one FMNMX (1 cycle) and one SHF (2 cycles) on the ALU pipe, measured by tools/pipebench.cu: SMs x 4 SMSPs x 32 lanes x clock / 3 cycles"},
         "roofline_demod": {"kernel": "demod_kernel", "bound": "hbm", "achieved": demod_bytes / (demod_ms * 1e-3) / 1e9, "peak": hbm_peak,
                            "unit": "GB/s", "frac": demod_bytes / (demod_ms * 1e-3) / 1e9 / hbm_peak},
         "signal_stage": sig_stage,
