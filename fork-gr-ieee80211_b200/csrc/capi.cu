@@ -25,6 +25,8 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <deque>
+#include <thread>
 #include <vector>
 #include "common.cuh"
 
@@ -41,12 +43,19 @@ struct PinBuf {
     size_t cap = 0;
 };
 
-enum { EV_START, EV_H2D, EV_HDR0, EV_HDR, EV_PLAN, EV_DEMOD, EV_VIT0, EV_VIT, EV_TB, EV_POST, EV_END, EV_COUNT };
+enum { EV_START, EV_COPIED, EV_H2D, EV_HDR0, EV_HDR, EV_HDRD, EV_PLAN, EV_DEMOD, EV_VIT0, EV_VIT, EV_TB, EV_POST, EV_END, EV_COUNT };
 
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[EV_COUNT] = {};
     bool busy = false;
+    /* rx_submit returns once the input copies and the header kernel are enqueued; the rest of the batch (host plan, demod,
+     * decode) is enqueued by a later API call, when the descriptors have arrived (run_continuation) */
+    int phase = 0;    /* 0 idle, 1 header stage enqueued, 2 everything enqueued */
+    int cont_err = 0; /* result of the continuation, reported by rx_collect */
+    const float2* c_iq[2] = {nullptr, nullptr};
+    const w80211_pkt_in* c_pk = nullptr;
+    int c_chan_stride = 64;
     /* device */
     DevBuf iq[2], iq_raw[2], pkts, chan_in, desc, chan, symprefix, llr, surv, bits, bytes, mpdus, counters, slot_pkt, pkt_slot, grp,
         dec_list, psdu_off;
@@ -86,6 +95,11 @@ struct w80211_ctx {
     int device = 0;
     int nslots = 2;
     cudaEvent_t origin = nullptr;    /* W80211_TRACE=1: time zero of the per-batch timelines printed by collect_slot */
+    std::deque<int> pending;         /* slots in phase 1, in submission order */
+    /* The input copies of all slots go through this one stream, so they reach the device one batch after the other at the
+     * full rate of the link; on the slots' own streams the copy engine would interleave them and every batch in flight
+     * would receive its last byte at about the same time. */
+    cudaStream_t cstream = nullptr;
     cudaEvent_t last_tail = nullptr; /* EV_POST of the batch whose decode was enqueued last (see enqueue_front) */
     W80211Tables* d_tab = nullptr;
     Slot slots[4];
@@ -281,17 +295,29 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     memcpy(hp + o_po, s.h_psdu_off.data(), sz_po);
     s.plan_o_psdu = o_po;
     cudaStream_t st = s.stream;
-    CK(cudaMemcpyAsync(s.symprefix.p, hp + o_sym, sz_sym, cudaMemcpyHostToDevice, st));
+    /* host-fed batches: later batches' input copies are already queued on the copy engine, so the plan goes up through a
+     * kernel that reads the pinned buffers; resident batches: the SMs may be busy, the copy engine is not */
+    const bool by_kernel = s.in_host && s.did_demod;
+    auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
+        if (bytes == 0) return cudaSuccess;
+        if (by_kernel) {
+            w_launch_upload(st, dst, src, bytes);
+            s.launches += 1;
+            return cudaGetLastError();
+        }
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+    };
+    CK(up(s.symprefix.p, hp + o_sym, sz_sym));
     if (do_decode) {
-        if (sz_sp) CK(cudaMemcpyAsync(s.slot_pkt.p, hp + o_sp, sz_sp, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(s.pkt_slot.p, hp + o_ps, sz_ps, cudaMemcpyHostToDevice, st));
-        if (sz_g) CK(cudaMemcpyAsync(s.grp.p, hp + o_g, sz_g, cudaMemcpyHostToDevice, st));
-        if (sz_d) CK(cudaMemcpyAsync(s.dec_list.p, hp + o_d, sz_d, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(s.psdu_off.p, hp + o_po, sz_po, cudaMemcpyHostToDevice, st));
+        CK(up(s.slot_pkt.p, hp + o_sp, sz_sp));
+        CK(up(s.pkt_slot.p, hp + o_ps, sz_ps));
+        CK(up(s.grp.p, hp + o_g, sz_g));
+        CK(up(s.dec_list.p, hp + o_d, sz_d));
+        CK(up(s.psdu_off.p, hp + o_po, sz_po));
         CK(cudaMemsetAsync(s.counters.p, 0, 64, st));
     }
     /* descriptors with their LLR offsets back to the device */
-    CK(cudaMemcpyAsync(s.desc.p, hd, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyHostToDevice, st));
+    CK(up(s.desc.p, hd, (size_t)npkt * sizeof(w80211_desc)));
     return 0;
 }
 
@@ -367,7 +393,9 @@ int finish_outputs(w80211_ctx* ctx, Slot& s)
 }
 
 /* front half shared by demod_batch and rx_submit */
-int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_batch_out* out, bool do_decode)
+/* first half of a batch: input copies (or nothing for device input), integer IQ expansion, header kernel, descriptors
+ * back to the host.  Does not wait. */
+int enqueue_input_header(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_batch_out* out, bool do_decode)
 {
     if (!in || !out || in->npkt < 0 || (in->nant != 1 && in->nant != 2) || !in->iq[0] || (in->nant == 2 && !in->iq[1]) ||
         (in->npkt > 0 && (!in->pkts || !in->chan)) || (in->iq_format != W80211_IQ_FC32 && in->iq_format != W80211_IQ_SC16 && in->iq_format != W80211_IQ_SC8))
@@ -393,23 +421,29 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
     const w80211_pkt_in* d_pk;
     const float2* d_chin;
     if (s.in_host) {
+        cudaStream_t cs = ctx->cstream ? ctx->cstream : st;
         RS(dev_reserve(ctx, s.pkts, (size_t)npkt * sizeof(w80211_pkt_in) + 16));
         RS(dev_reserve(ctx, s.chan_in, (size_t)npkt * 512 + 16));
+        for (int a = 0; a < in->nant; a++) {
+            RS(dev_reserve(ctx, s.iq[a], (size_t)in->nsamples * 8 + 1024));
+            if (sc16) RS(dev_reserve(ctx, s.iq_raw[a], (size_t)in->nsamples * raw_bytes + 1024));
+        }
         if (npkt) {
-            CK(cudaMemcpyAsync(s.pkts.p, in->pkts, (size_t)npkt * sizeof(w80211_pkt_in), cudaMemcpyHostToDevice, st));
-            CK(cudaMemcpyAsync(s.chan_in.p, in->chan, (size_t)npkt * 512, cudaMemcpyHostToDevice, st));
+            CK(cudaMemcpyAsync(s.pkts.p, in->pkts, (size_t)npkt * sizeof(w80211_pkt_in), cudaMemcpyHostToDevice, cs));
+            CK(cudaMemcpyAsync(s.chan_in.p, in->chan, (size_t)npkt * 512, cudaMemcpyHostToDevice, cs));
         }
         d_pk = (const w80211_pkt_in*)s.pkts.p;
         d_chin = (const float2*)s.chan_in.p;
         for (int a = 0; a < in->nant; a++) {
-            RS(dev_reserve(ctx, s.iq[a], (size_t)in->nsamples * 8 + 1024));
-            if (sc16) {
-                RS(dev_reserve(ctx, s.iq_raw[a], (size_t)in->nsamples * raw_bytes + 1024));
-                CK(cudaMemcpyAsync(s.iq_raw[a].p, in->iq[a], (size_t)in->nsamples * raw_bytes, cudaMemcpyHostToDevice, st));
-            } else {
-                CK(cudaMemcpyAsync(s.iq[a].p, in->iq[a], (size_t)in->nsamples * 8, cudaMemcpyHostToDevice, st));
-            }
+            if (sc16)
+                CK(cudaMemcpyAsync(s.iq_raw[a].p, in->iq[a], (size_t)in->nsamples * raw_bytes, cudaMemcpyHostToDevice, cs));
+            else
+                CK(cudaMemcpyAsync(s.iq[a].p, in->iq[a], (size_t)in->nsamples * 8, cudaMemcpyHostToDevice, cs));
             d_iq[a] = (const float2*)s.iq[a].p;
+        }
+        if (cs != st) {
+            CK(cudaEventRecord(s.ev[EV_COPIED], cs));
+            CK(cudaStreamWaitEvent(st, s.ev[EV_COPIED], 0));
         }
         if (sc16) {
             w_launch_sc16_to_fc32(st, npkt, in->nant, d_pk, s.iq_raw[0].p, s.iq_raw[1].p, (float2*)s.iq[0].p, (float2*)s.iq[1].p,
@@ -446,7 +480,23 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
     if (npkt) s.launches += 1;
     CK(cudaEventRecord(s.ev[EV_HDR], st));
     if (npkt) CK(cudaMemcpyAsync(s.h_desc.p, s.desc.p, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    CK(cudaEventRecord(s.ev[EV_HDRD], st));
+    s.c_iq[0] = d_iq[0];
+    s.c_iq[1] = d_iq[1];
+    s.c_pk = d_pk;
+    s.c_chan_stride = chan_stride;
+    return 0;
+}
+
+/* second half of the front: the descriptors are on the host (EV_HDRD has completed); plan, then demod */
+int continue_front(w80211_ctx* ctx, Slot& s)
+{
+    cudaStream_t st = s.stream;
+    const int npkt = s.npkt;
+    const bool do_decode = s.did_decode;
+    const float2* const* d_iq = s.c_iq;
+    const w80211_pkt_in* d_pk = s.c_pk;
+    const int chan_stride = s.c_chan_stride;
     w80211_desc* hd = (w80211_desc*)s.h_desc.p;
     const auto tp0 = std::chrono::steady_clock::now();
     RS(plan_and_upload(ctx, s, hd, true, do_decode));
@@ -461,7 +511,7 @@ int enqueue_front(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_ba
      * happen while the other slot's Viterbi kernel runs. */
     if (ctx->last_tail && ctx->last_tail != s.ev[EV_POST]) CK(cudaStreamWaitEvent(st, ctx->last_tail, 0));
     CK(cudaEventRecord(s.ev[EV_PLAN], st));
-    w_launch_demod(st, ctx->d_tab, s.nsymtot, npkt, in->nant, d_iq[0], d_iq[1], d_pk, (const w80211_desc*)s.desc.p,
+    w_launch_demod(st, ctx->d_tab, s.nsymtot, npkt, s.nant, d_iq[0], d_iq[1], d_pk, (const w80211_desc*)s.desc.p,
                    (const int*)s.symprefix.p, (const float2*)s.chan.p, chan_stride, (float*)s.llr.p);
     CK(cudaGetLastError());
     if (s.nsymtot) s.launches += 1;
@@ -581,6 +631,36 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
     return 0;
 }
 
+
+/* second half of a batch whose header stage has completed */
+void run_continuation(w80211_ctx* ctx, Slot& s)
+{
+    int r = continue_front(ctx, s);
+    if (r == 0 && s.did_decode) r = enqueue_decode_tail(ctx, s);
+    if (r == 0) r = finish_outputs(ctx, s);
+    s.cont_err = r;
+    s.phase = 2;
+}
+
+/* Enqueue the second half of every pending batch, in submission order, whose descriptors have reached the host.
+ * upto >= 0: wait for the descriptors of the batches up to and including slot `upto`; -2: of all of them. */
+void progress(w80211_ctx* ctx, int upto)
+{
+    while (!ctx->pending.empty()) {
+        const int idx = ctx->pending.front();
+        Slot& s = ctx->slots[idx];
+        if (upto == -1) {
+            if (cudaEventQuery(s.ev[EV_HDRD]) == cudaErrorNotReady) break;
+        } else {
+            cudaEventSynchronize(s.ev[EV_HDRD]);
+        }
+        ctx->pending.pop_front();
+        run_continuation(ctx, s);
+        if (idx == upto) upto = -1;
+    }
+    cudaGetLastError();
+}
+
 } // namespace
 
 extern "C" {
@@ -630,6 +710,7 @@ int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
     bool ok = cudaMalloc(&ctx->d_tab, sizeof(W80211Tables)) == cudaSuccess &&
               cudaMemcpy(ctx->d_tab, ht, sizeof(W80211Tables), cudaMemcpyHostToDevice) == cudaSuccess;
     delete ht;
+    ok = ok && cudaStreamCreateWithFlags(&ctx->cstream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < ctx->nslots; i++) {
         ok = cudaStreamCreateWithFlags(&ctx->slots[i].stream, cudaStreamNonBlocking) == cudaSuccess;
         for (int e = 0; ok && e < EV_COUNT; e++) ok = cudaEventCreate(&ctx->slots[i].ev[e]) == cudaSuccess;
@@ -648,6 +729,7 @@ void w80211_destroy(w80211_ctx* ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
+    if (ctx->cstream) cudaStreamSynchronize(ctx->cstream);
     for (int i = 0; i < 4; i++) {
         Slot& s = ctx->slots[i];
         if (s.stream) cudaStreamSynchronize(s.stream);
@@ -677,6 +759,7 @@ void w80211_destroy(w80211_ctx* ctx)
             if (e) cudaEventDestroy(e);
         if (g.stream) cudaStreamDestroy(g.stream);
     }
+    if (ctx->cstream) cudaStreamDestroy(ctx->cstream);
     if (ctx->origin) cudaEventDestroy(ctx->origin);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
     delete ctx;
@@ -724,22 +807,43 @@ int w80211_rx_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w8021
     if (!ctx) return W80211_E_ARG;
     if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
     Slot& s = ctx->slots[slot];
-    RS(enqueue_front(ctx, s, in, out, true));
-    s.busy = true;
-    int r = enqueue_decode_tail(ctx, s);
-    if (r == 0) r = finish_outputs(ctx, s);
+    progress(ctx, -1);
+    int r = enqueue_input_header(ctx, s, in, out, true);
     if (r < 0) {
-        cudaStreamSynchronize(s.stream);
-        s.busy = false;
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        return r;
     }
-    return r;
+    s.busy = true;
+    s.phase = 1;
+    s.cont_err = 0;
+    ctx->pending.push_back(slot);
+    return W80211_OK;
 }
 
 int w80211_rx_collect(w80211_ctx* ctx, int slot)
 {
     if (!ctx) return W80211_E_ARG;
     if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
-    return collect_slot(ctx, ctx->slots[slot]);
+    Slot& s = ctx->slots[slot];
+    if (!s.busy) return fail(ctx, W80211_E_STATE, "slot idle: nothing to collect");
+    CK(cudaSetDevice(ctx->device));
+    if (s.phase == 1) progress(ctx, slot);
+    /* wait for this batch, and meanwhile enqueue the second half of any other batch whose descriptors arrive */
+    while (!ctx->pending.empty()) {
+        progress(ctx, -1);
+        cudaError_t q = cudaStreamQuery(s.stream);
+        if (q != cudaErrorNotReady) break;
+        std::this_thread::sleep_for(std::chrono::microseconds(20));
+    }
+    if (s.cont_err < 0) {
+        cudaStreamSynchronize(s.stream);
+        s.busy = false;
+        s.phase = 0;
+        return s.cont_err;
+    }
+    int r = collect_slot(ctx, s);
+    s.phase = 0;
+    return r;
 }
 
 int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out)
@@ -1123,9 +1227,12 @@ int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_
 {
     if (!ctx) return W80211_E_ARG;
     Slot& s = ctx->slots[0];
-    RS(enqueue_front(ctx, s, in, out, false));
+    progress(ctx, -2);
+    RS(enqueue_input_header(ctx, s, in, out, false));
     s.busy = true;
-    int r = finish_outputs(ctx, s);
+    int r = cudaEventSynchronize(s.ev[EV_HDRD]) == cudaSuccess ? 0 : fail(ctx, W80211_E_CUDA, "header stage failed");
+    if (r == 0) r = continue_front(ctx, s);
+    if (r == 0) r = finish_outputs(ctx, s);
     if (r < 0) {
         cudaStreamSynchronize(s.stream);
         s.busy = false;
@@ -1142,6 +1249,7 @@ int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, 
     Slot& s = ctx->slots[0];
     if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy");
     CK(cudaSetDevice(ctx->device));
+    progress(ctx, -2);
     cudaStream_t st = s.stream;
     s.npkt = npkt;
     s.out = out;

@@ -218,6 +218,7 @@ void w_launch_cfo_copy(cudaStream_t st, int npkt, int nant, int max_nsamp, const
                        const float2* in1, float2* out0, float2* out1, const float2* chan_all, float2* chan_out);
 void w_launch_sc16_to_fc32(cudaStream_t st, int npkt, int nant, const w80211_pkt_in* pkts, const void* raw0, const void* raw1,
                            float2* out0, float2* out1, unsigned long long nsamples, int bytes_per_sample);
+void w_launch_upload(cudaStream_t st, void* dst, const void* pinned_src, size_t bytes);
 int w_launch_viterbi(cudaStream_t st, const int* cr_first, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
                      const float* llr, uint2* surv);
 void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,

@@ -6,6 +6,7 @@
  * sample = ((float)re * scale, (float)im * scale) -- int16 -> binary32 is exact and the multiply is one rounded
  * binary32 operation, the same a host would do, so the reference fed those products sees identical input.
  * One block per packet; 4 bytes read and 8 written per sample, coalesced. */
+#include <algorithm>
 #include "common.cuh"
 
 template <class RAW>
@@ -79,4 +80,19 @@ void w_launch_cfo_copy(cudaStream_t st, int npkt, int nant, int max_nsamp, const
     if (npkt <= 0) return;
     dim3 grid(npkt, max(1, (max_nsamp + CFO_CHUNK - 1) / CFO_CHUNK));
     cfo_copy_kernel<<<grid, 256, 0, st>>>(npkt, nant, acc, in0, in1, out0, out1, chan_all, chan_out);
+}
+
+/* Small host -> device uploads (the host plan of a batch) done by a kernel that reads the pinned host buffer directly:
+ * on the copy engine they would queue behind the gigabytes of input samples that later batches have already enqueued. */
+__global__ void __launch_bounds__(256) upload_words_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, size_t nwords)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+void w_launch_upload(cudaStream_t st, void* dst, const void* pinned_src, size_t bytes)
+{
+    if (bytes == 0) return;
+    const size_t nwords = (bytes + 3) / 4; /* every plan array is a whole number of 32-bit words in buffers padded beyond that */
+    int blocks = (int)std::min<size_t>((nwords + 255) / 256, 1184);
+    upload_words_kernel<<<blocks, 256, 0, st>>>((uint32_t*)dst, (const uint32_t*)pinned_src, nwords);
 }
