@@ -298,9 +298,13 @@ int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_
 int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, const float* llr,
                         uint64_t nllr, int32_t llr_mem, w80211_batch_out* out);
 
-/* Fused path: IQ -> bytes, LLRs stay in HBM.  submit() enqueues copies and kernels on slot's stream
- * and returns; collect() waits for the slot and fills the host-side counters of *out.
- * rx_batch() = submit + collect on slot 0. */
+/* Fused path: IQ -> bytes, LLRs stay in HBM.  submit() enqueues the input copies and the header stage on the slot's
+ * stream and returns without waiting; the rest of the batch (host plan, demod, decode, result copies) is enqueued by
+ * the next call of submit() / collect() on this context that finds the header stage finished, in submission order, so a
+ * caller that keeps 2-4 slots in flight never blocks on a copy.  *in's arrays and *out must stay valid until collect(),
+ * which waits for the slot, reports any error of that second half and fills the host-side counters of *out.
+ * Device-resident results (out->mem = W80211_MEM_DEVICE) are written straight into out->bytes when it is 16-byte
+ * aligned.  rx_batch() = submit + collect on slot 0. */
 int w80211_rx_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w80211_batch_out* out);
 int w80211_rx_collect(w80211_ctx* ctx, int slot);
 int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out);
