@@ -313,6 +313,23 @@ class Receiver:
         self._check(self.L.w80211_rx_batch(self.h, C.byref(bi), C.byref(bo)))
         return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo, arrs["llr"])
 
+    def submit(self, slot, iq, pkts, chan, want_llr=False, mu_pos=0, bytes_cap=None):
+        """IQ -> bytes on slot `slot` without waiting (w80211_rx_submit); collect(slot) returns the Result."""
+        bcap, mcap, lcap = self._caps(iq, pkts)
+        bi = self.make_in(iq, pkts, chan, mu_pos=mu_pos)
+        bo, arrs = self.make_out_host(len(pkts), bcap if bytes_cap is None else bytes_cap, mcap, lcap if want_llr else 0)
+        keep = (bi, bo, arrs, iq, pkts, chan)  # the library reads them until collect()
+        self._check(self.L.w80211_rx_submit(self.h, slot, C.byref(bi), C.byref(bo)))
+        self._keep[slot] = keep
+
+    def collect(self, slot):
+        try:
+            self._check(self.L.w80211_rx_collect(self.h, slot))
+            bi, bo, arrs = self._keep[slot][:3]
+            return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo, arrs["llr"])
+        finally:
+            self._keep.pop(slot, None)
+
     def demod(self, iq, pkts, chan, mu_pos=0):
         """IQ -> LLR stream + descriptors (w80211_demod_batch): what demod / demod2 output."""
         bcap, mcap, lcap = self._caps(iq, pkts)

@@ -247,3 +247,57 @@ def test_garbage_sig_fields_take_the_reference_decisions(refgr, rx):
     st = np.asarray(res.desc["status"])
     assert (st == host.ST_OK).sum() >= 1400  # the legacy fall-through
     assert len(msgs) <= 5
+
+
+def test_slots_in_flight_equal_one_batch_at_a_time():
+    """w80211_rx_submit / rx_collect with four slots in flight: submit() returns before the header stage has finished and
+    the second half of every batch is enqueued by later calls, in submission order; results equal w80211_rx_batch's."""
+    rx4 = host.Receiver(0, nslots=4)
+    try:
+        batches = [gp.gen_batch(g.F_L, 7, 1, 700, 5, snr_db=30, seed=70), gp.gen_batch(g.F_HT, 7, 1, 1200, 4, snr_db=30, short_gi=True, seed=71),
+                   gp.gen_batch(g.F_VHT, 8, 1, 2000, 3, snr_db=30, seed=72), gp.gen_batch(g.F_HT, 12, 2, 900, 3, snr_db=35, seed=73),
+                   gp.gen_batch(g.F_L, 0, 1, 94, 6, snr_db=20, seed=74), gp.gen_batch(g.F_VHT, 3, 1, 333, 2, snr_db=30, seed=75)]
+        packed = [host.pack_batch([b]) for b in batches]
+        alone = [rx4.rx(*p, want_llr=True) for p in packed]
+        got = [None] * len(packed)
+        for rounds in range(2):  # twice: slots are reused
+            pend = []
+            for i, p in enumerate(packed):
+                s = i % 4
+                if len(pend) == 4:
+                    j = pend.pop(0)
+                    got[j] = rx4.collect(j % 4)
+                rx4.submit(s, *p, want_llr=True)
+                pend.append(i)
+            for j in pend:
+                got[j] = rx4.collect(j % 4)
+            for a, b2, bt in zip(alone, got, batches):
+                assert b2.messages() == a.messages() and len(a.messages()) == len(bt["mpdu"])
+                assert np.array_equal(b2.desc, a.desc)
+                for q in range(len(a.desc)):  # (the gaps between packets in the LLR buffer are not written)
+                    assert np.array_equal(b2.packet_llr(q), a.packet_llr(q))
+                assert np.array_equal(b2.mpdus[: b2.n_mpdu], a.mpdus[: a.n_mpdu])
+    finally:
+        rx4.close()
+
+
+def test_submit_collect_errors_leave_the_slot_usable():
+    rx2 = host.Receiver(0, nslots=2)
+    try:
+        b = gp.gen_batch(g.F_L, 5, 1, 400, 3, snr_db=30, seed=80)
+        p = host.pack_batch([b])
+        with pytest.raises(host.W80211Error):
+            rx2.collect(0)  # nothing submitted
+        rx2.submit(0, *p)
+        with pytest.raises(host.W80211Error):
+            rx2.submit(0, *p)  # busy
+        ok = rx2.collect(0)
+        assert len(ok.messages()) == 3
+        # an error of the second half (output buffer too small) is reported by collect(); the slot works again afterwards
+        rx2.submit(1, *p, bytes_cap=16)
+        with pytest.raises(host.W80211Error):
+            rx2.collect(1)
+        rx2.submit(1, *p)
+        assert rx2.collect(1).messages() == ok.messages()
+    finally:
+        rx2.close()
