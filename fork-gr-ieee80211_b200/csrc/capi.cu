@@ -14,8 +14,10 @@
  *   post kernel     -> PSDU bytes, MPDU records, counters   post.cu
  *   D2H(bytes, records, counters)
  *
- * The only host synchronisation inside a batch is the one after the header kernel; with two slots
- * the GPU works on one batch while the host plans the other.
+ * The host plan is the only host step inside a batch, and no call waits for it: rx_submit() returns after enqueueing
+ * the header stage, and the second half of the batch is enqueued by the next API call that finds the descriptors on the
+ * host (progress()).  With several slots in flight a batch's demod kernel waits for the previous batch's traceback and
+ * post kernels, so the slots alternate and one slot's host work hides behind the other's Viterbi kernel.
  */
 #include <algorithm>
 #include <chrono>
@@ -178,10 +180,6 @@ inline long long llr_needed(int trellis, int cr)
     if (rem > 0) n += 2 + (rem - 1);
     return n;
 }
-
-struct Plan {
-    std::vector<int> order;
-};
 
 /* Host plan after the header stage.  Fills llr offsets in h_desc, uploads the plan arrays. */
 int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, bool do_decode)
