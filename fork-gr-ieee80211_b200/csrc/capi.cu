@@ -201,7 +201,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
         } else if (assign_llr) {
             d.llr_off = -1;
         }
-        symprefix[p + 1] = symprefix[p] + (nsym + 7) / 8; /* demod work items: chunks of DEMOD_SPC = 8 symbols */
+        symprefix[p + 1] = symprefix[p] + (nsym + W_DEMOD_SPC - 1) / W_DEMOD_SPC; /* demod work items: runs of W_DEMOD_SPC symbols */
     }
     if (assign_llr) s.n_llr = off;
     s.nsymtot = symprefix[npkt];

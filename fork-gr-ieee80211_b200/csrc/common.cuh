@@ -21,6 +21,9 @@
 #define W_WARP 32
 #define W_NMAPS 19
 #define W_MAPLEN 416
+#ifndef W_DEMOD_SPC
+#define W_DEMOD_SPC 36 /* most symbols per demod work item (one 8-lane group walks them in order); the host plan counts items with it */
+#endif
 #define W_XPOW8 4224
 
 /* Constant tables, generated on the host from the 802.11 formulas (tables.cc)

@@ -8,7 +8,7 @@
  *   procSymQamToLlr               cloud80211phy.cc:2090-2148   max-log LLRs, I bits then Q bits
  *   procSymDeintL2 / NL2SS1 / NL2SS2, procSymDepasNL  :2150-2338, :2442-2451  (folded into one index table)
  * The running state of the reference (pilot polarity index, pilot rotation) is a closed form of the
- * symbol number here, so symbols are independent.  A work item is a run of up to 8 symbols of one packet, walked by one
+ * symbol number here, so symbols are independent.  A work item is a run of up to W_DEMOD_SPC symbols of one packet, walked by one
  * 8-lane group with the next symbol's samples prefetched; reads: nRx * 64 complex samples per
  * symbol (coalesced 64-byte segments); the symbol's nCBPS LLRs are scattered (deinterleaved) into
  * shared memory and leave as coalesced 16-byte vectors.
@@ -20,12 +20,15 @@
 #define DEMOD_MINBLK 8
 #endif
 #define DEMOD_GROUPS (DEMOD_THREADS / 8)
-#define DEMOD_SPC 8        /* symbols per work item (one 8-lane group walks them in order) */
+#define DEMOD_SPC W_DEMOD_SPC /* most symbols per work item (one 8-lane group walks them in order) */
 #define DEMOD_STAGE 832    /* floats: largest nCBPS (2 streams of 256-QAM) */
 #define DEMOD_PAD 2        /* floats after a group's staging row: rows start 2 banks apart (the deinterleaved positions of the
                               8 bins a group writes at a time fall on 8 banks that repeat every row of 416 / 832 floats), and
                               the pad is the slot that bins without data write to */
 #define DEMOD_MAPPAD 8     /* map entries after a table, all pointing at that slot */
+#ifndef DEMOD_COPY_BATCH
+#define DEMOD_COPY_BATCH 0
+#endif
 #ifndef DEMOD_NOHOIST
 #define DEMOD_NOHOIST 1
 #endif
@@ -226,8 +229,12 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     if (valid) {
         p = find_packet(item_prefix, npkt, nitems, w);
         const w80211_desc* d = &desc[p];
-        n0 = (w - __ldg(&item_prefix[p])) * DEMOD_SPC;
-        nsy = min(DEMOD_SPC, d->nsym - n0);
+        /* the packet's symbols are dealt out evenly over its items (105 symbols, 3 items: 35 each, not 36 + 36 + 33), so
+         * the four groups of a warp, which loop together, finish together */
+        const int first = __ldg(&item_prefix[p]), nit = __ldg(&item_prefix[p + 1]) - first;
+        const int per = (d->nsym + nit - 1) / nit;
+        n0 = (w - first) * per;
+        nsy = max(0, min(per, d->nsym - n0));
         fmt = d->format;
         nss = d->nss;
         nb = d->nbpscs;
@@ -407,7 +414,21 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             /* the symbol's nCBPS floats leave as 8-byte vectors (rows are 8-byte aligned), 64 contiguous bytes per group and store */
             float2* out2 = reinterpret_cast<float2*>(llr + llr_off + (size_t)n * ncbps);
             const float2* s2 = reinterpret_cast<const float2*>(stg);
+#if DEMOD_COPY_BATCH
+            /* eight loads, then eight stores: the shared-memory latency is paid once per batch */
+            const int n2 = ncbps >> 1;
+            for (int k0 = g; k0 < n2; k0 += 64) {
+                float2 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++)
+                    if (k0 + 8 * u < n2) v[u] = s2[k0 + 8 * u];
+#pragma unroll
+                for (int u = 0; u < 8; u++)
+                    if (k0 + 8 * u < n2) out2[k0 + 8 * u] = v[u];
+            }
+#else
             for (int k = g; k < (ncbps >> 1); k += 8) out2[k] = s2[k];
+#endif
         }
         __syncwarp();
 #pragma unroll
