@@ -75,6 +75,7 @@ struct Slot {
     std::vector<uint32_t> h_psdu_off;
     /* host plan scratch, kept between batches (a fresh 0.5 MB vector per array and batch costs page faults) */
     std::vector<int> v_symprefix, v_dec, v_slot_pkt, v_pkt_slot;
+    std::vector<uint32_t> v_key;
     std::vector<int4> v_grp;
     w80211_timing timing = {};
     float host_plan_ms = 0.f;
@@ -185,10 +186,18 @@ inline long long llr_needed(int trellis, int cr)
 int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, bool do_decode)
 {
     const int npkt = s.npkt;
-    /* LLR layout and symbol prefix sums */
+    /* One pass over the descriptors (12 MB for a full batch; the later loops only touch a 4-byte key per packet): LLR
+     * layout, symbol prefix sums, and the packets to decode with their sort key (code rate ascending, trellis descending). */
     uint64_t off = 0;
     std::vector<int>& symprefix = s.v_symprefix;
     symprefix.assign((size_t)npkt + 1, 0);
+    std::vector<int>& dec = s.v_dec;
+    std::vector<uint32_t>& key = s.v_key;
+    dec.clear();
+    key.assign((size_t)npkt, 0);
+    s.trellis_steps = 0;
+    bool sorted = true;
+    uint32_t last_key = 0;
     for (int p = 0; p < npkt; p++) {
         w80211_desc& d = hd[p];
         int nsym = 0;
@@ -202,31 +211,21 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
             d.llr_off = -1;
         }
         symprefix[p + 1] = symprefix[p] + (nsym + W_DEMOD_SPC - 1) / W_DEMOD_SPC; /* demod work items: runs of W_DEMOD_SPC symbols */
+        if (!do_decode || d.status != W80211_ST_OK) continue;
+        /* decode_impl.cc:93: len > 4095 or trellis > 32782 -> skipped */
+        if (d.len > W80211_B_MAX || d.len < 0 || d.trellis > W80211_T_MAX || d.trellis <= 0) continue;
+        if (d.cr < 0 || d.cr > 3 || d.llr_off < 0 || (d.llr_off & 3)) continue;
+        if (llr_needed(d.trellis, d.cr) > (long long)d.total) continue;
+        const uint32_t k = ((uint32_t)d.cr << 16) | (uint32_t)(0xffff - d.trellis);
+        key[p] = k;
+        sorted = sorted && k >= last_key;
+        last_key = k;
+        dec.push_back(p);
+        s.trellis_steps += (uint64_t)d.trellis;
     }
     if (assign_llr) s.n_llr = off;
     s.nsymtot = symprefix[npkt];
-
-    /* packets to decode, sorted by (code rate, trellis descending) */
-    std::vector<int>& dec = s.v_dec;
-    dec.clear();
-    s.trellis_steps = 0;
-    if (do_decode) {
-        for (int p = 0; p < npkt; p++) {
-            const w80211_desc& d = hd[p];
-            if (d.status != W80211_ST_OK) continue;
-            /* decode_impl.cc:93: len > 4095 or trellis > 32782 -> skipped */
-            if (d.len > W80211_B_MAX || d.len < 0 || d.trellis > W80211_T_MAX || d.trellis <= 0) continue;
-            if (d.cr < 0 || d.cr > 3 || d.llr_off < 0 || (d.llr_off & 3)) continue;
-            if (llr_needed(d.trellis, d.cr) > (long long)d.total) continue;
-            dec.push_back(p);
-            s.trellis_steps += (uint64_t)d.trellis;
-        }
-        auto before = [&](int a, int b) {
-            if (hd[a].cr != hd[b].cr) return hd[a].cr < hd[b].cr;
-            return hd[a].trellis > hd[b].trellis;
-        };
-        if (!std::is_sorted(dec.begin(), dec.end(), before)) std::stable_sort(dec.begin(), dec.end(), before); /* homogeneous batches: nothing to do */
-    }
+    if (!sorted) std::stable_sort(dec.begin(), dec.end(), [&](int a2, int b2) { return key[a2] < key[b2]; }); /* homogeneous batches: nothing to do */
     s.ndec = (int)dec.size();
     std::vector<int>&slot_pkt = s.v_slot_pkt, &pkt_slot = s.v_pkt_slot;
     std::vector<int4>& grp = s.v_grp;
@@ -237,17 +236,21 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     uint64_t row = 0, wrow = 0, boff = 0;
     for (int c = 0; c <= 4; c++) s.cr_first[c] = 0;
     for (size_t i = 0; i < dec.size();) {
-        int cr = hd[dec[i]].cr;
-        int maxT = hd[dec[i]].trellis;
+        const int cr = (int)(key[dec[i]] >> 16);
+        const int maxT = 0xffff - (int)(key[dec[i]] & 0xffffu);
         int4 G;
         G.x = (int)row;
         G.y = (maxT + 1) & ~1;
         G.z = (int)wrow;
         G.w = cr;
         int k = 0;
-        for (; k < 32 && i < dec.size() && hd[dec[i]].cr == cr; k++, i++) {
-            pkt_slot[dec[i]] = (int)slot_pkt.size();
-            slot_pkt.push_back(dec[i]);
+        for (; k < 32 && i < dec.size() && (int)(key[dec[i]] >> 16) == cr; k++, i++) {
+            const int p = dec[i];
+            pkt_slot[p] = (int)slot_pkt.size();
+            slot_pkt.push_back(p);
+            s.h_psdu_off[p] = (uint32_t)boff; /* output bytes in decode order */
+            const int T = 0xffff - (int)(key[p] & 0xffffu);
+            boff += align_up((size_t)((T - 16 + 7) / 8) + 8, 16);
         }
         for (; k < 32; k++) slot_pkt.push_back(-1);
         for (int c = cr + 1; c <= 4; c++) s.cr_first[c] = (int)grp.size() + 1;
@@ -255,10 +258,6 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
         row += (uint64_t)G.y;
         wrow += (uint64_t)((maxT + 31) >> 5);
         if (row > 0x7fffffffull) return fail(ctx, W80211_E_CAPACITY, "batch too large: survivor rows overflow");
-    }
-    for (int p : dec) {
-        s.h_psdu_off[p] = (uint32_t)boff;
-        boff += align_up((size_t)((hd[p].trellis - 16 + 7) / 8) + 8, 16);
         if (boff > 0xffffffffull) return fail(ctx, W80211_E_CAPACITY, "batch too large: output bytes overflow 4 GiB");
     }
     s.n_bytes = boff;
