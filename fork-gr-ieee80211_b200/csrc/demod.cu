@@ -22,9 +22,11 @@
 #define DEMOD_GROUPS (DEMOD_THREADS / 8)
 #define DEMOD_SPC W_DEMOD_SPC /* most symbols per work item (one 8-lane group walks them in order) */
 #define DEMOD_STAGE 832    /* floats: largest nCBPS (2 streams of 256-QAM) */
-#define DEMOD_PAD 2        /* floats after a group's staging row: rows start 2 banks apart (the deinterleaved positions of the
-                              8 bins a group writes at a time fall on 8 banks that repeat every row of 416 / 832 floats), and
-                              the pad is the slot that bins without data write to */
+#ifndef DEMOD_PAD
+#define DEMOD_PAD 4        /* floats after a group's staging row: rows start 4 banks apart (the deinterleaved positions of the
+                              8 bins a group writes at a time fall on 8 banks that repeat every row of 416 / 832 floats) and
+                              stay 16-byte aligned for the copy-out; the pad is the slot that bins without data write to */
+#endif
 #define DEMOD_MAPPAD 8     /* map entries after a table, all pointing at that slot */
 #ifndef DEMOD_COPY_BATCH
 #define DEMOD_COPY_BATCH 0
@@ -411,7 +413,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
         }
         __syncwarp();
         if (act) {
-            /* the symbol's nCBPS floats leave as 8-byte vectors (rows are 8-byte aligned), 64 contiguous bytes per group and store */
+            /* the symbol's nCBPS floats leave as 16-byte vectors when the rows are 16-byte aligned (128 contiguous bytes per
+             * group and store), else as 8-byte vectors */
             float2* out2 = reinterpret_cast<float2*>(llr + llr_off + (size_t)n * ncbps);
             const float2* s2 = reinterpret_cast<const float2*>(stg);
 #if DEMOD_COPY_BATCH
@@ -427,7 +430,13 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
                     if (k0 + 8 * u < n2) out2[k0 + 8 * u] = v[u];
             }
 #else
+#if DEMOD_PAD % 4 == 0
+            float4* out4 = reinterpret_cast<float4*>(out2);
+            const float4* s4 = reinterpret_cast<const float4*>(stg);
+            for (int k = g; k < (ncbps >> 2); k += 8) out4[k] = s4[k];
+#else
             for (int k = g; k < (ncbps >> 1); k += 8) out2[k] = s2[k];
+#endif
 #endif
         }
         __syncwarp();
