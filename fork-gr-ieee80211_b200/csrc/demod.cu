@@ -28,9 +28,6 @@
                               stay 16-byte aligned for the copy-out; the pad is the slot that bins without data write to */
 #endif
 #define DEMOD_MAPPAD 8     /* map entries after a table, all pointing at that slot */
-#ifndef DEMOD_COPY_BATCH
-#define DEMOD_COPY_BATCH 0
-#endif
 #ifndef DEMOD_NOHOIST
 #define DEMOD_NOHOIST 1
 #endif
@@ -417,26 +414,12 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
              * group and store), else as 8-byte vectors */
             float2* out2 = reinterpret_cast<float2*>(llr + llr_off + (size_t)n * ncbps);
             const float2* s2 = reinterpret_cast<const float2*>(stg);
-#if DEMOD_COPY_BATCH
-            /* eight loads, then eight stores: the shared-memory latency is paid once per batch */
-            const int n2 = ncbps >> 1;
-            for (int k0 = g; k0 < n2; k0 += 64) {
-                float2 v[8];
-#pragma unroll
-                for (int u = 0; u < 8; u++)
-                    if (k0 + 8 * u < n2) v[u] = s2[k0 + 8 * u];
-#pragma unroll
-                for (int u = 0; u < 8; u++)
-                    if (k0 + 8 * u < n2) out2[k0 + 8 * u] = v[u];
-            }
-#else
 #if DEMOD_PAD % 4 == 0
             float4* out4 = reinterpret_cast<float4*>(out2);
             const float4* s4 = reinterpret_cast<const float4*>(stg);
             for (int k = g; k < (ncbps >> 2); k += 8) out4[k] = s4[k];
 #else
             for (int k = g; k < (ncbps >> 1); k += 8) out2[k] = s2[k];
-#endif
 #endif
         }
         __syncwarp();
