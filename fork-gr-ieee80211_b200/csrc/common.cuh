@@ -44,6 +44,7 @@ struct W80211Tables {
     uint32_t crc_tab[4][256];
     uint32_t crc_x2n[32];
     uint32_t crc_xpow8[W_XPOW8]; /* x^(8n) mod P, n = 0 .. W_XPOW8-1 bytes */
+    uint32_t scr_seq[128][8];    /* descrambler: 160 output bits of x^7+x^4+1 started from 7-bit state s, bit k of word k/32; words 5..7 = 0 */
 };
 
 struct cf32 {

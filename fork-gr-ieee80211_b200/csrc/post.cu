@@ -3,8 +3,8 @@
  * Replaces decode_impl::descramble (lib/decode_impl.cc:304-323) and decode_impl::packetAssemble
  * (:325-520) including the boost::crc_32_type check (decode_impl.h:84, :372-374, :451-453).
  *
- *  - descramble: the 7-bit scrambler state is read from the first 7 decoded bits; the x^7+x^4+1
- *    sequence is generated once per packet (160 bits) and applied 32 bits at a time;
+ *  - descramble: the 7-bit scrambler state is read from the first 7 decoded bits; the 160 bits of the x^7+x^4+1
+ *    sequence that follow it come from a table made on the host and are applied 32 bits at a time;
  *  - bytes: LSB first from bit 16, i.e. the descrambled bit words viewed as bytes, offset 2;
  *  - CRC-32 (reflected 0xEDB88320, init/xorout 0xFFFFFFFF): every lane runs a four-bytes-per-step table CRC
  *    (tables made on the host, tables.cc) over its own slice of the MPDU, the 32 partial CRCs are merged with
@@ -129,21 +129,12 @@ __global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(const W80211Table
 
     /* scrambler state from the first 7 bits (decode_impl.cc:308-314), then 160 sequence bits */
     uint32_t w0 = __ldg(src);
-    if (lane == 0) {
+    {
+        /* the 160 sequence bits of this state come from the host-made table (tables.cc), six words per warp */
         int state = 0;
         for (int i = 0; i < 7; i++)
             if ((w0 >> i) & 1u) state |= 1 << (6 - i);
-        uint32_t acc = 0;
-        for (int k = 0; k < 160; k++) {
-            int fb = ((state >> 6) & 1) ^ ((state >> 3) & 1);
-            state = ((state << 1) & 0x7e) | fb;
-            acc |= (uint32_t)fb << (k & 31);
-            if ((k & 31) == 31) {
-                S.seq[wid][k >> 5] = acc;
-                acc = 0;
-            }
-        }
-        S.seq[wid][5] = 0;
+        if (lane < 6) S.seq[wid][lane] = __ldg(&tab->scr_seq[state][lane]);
     }
     __syncwarp();
     const uint32_t* seq = S.seq[wid];

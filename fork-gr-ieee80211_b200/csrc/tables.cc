@@ -46,6 +46,15 @@ void w80211_fill_tables(W80211Tables* t)
         for (int i = 0; i < 256; i++) t->crc_tab[s][i] = (t->crc_tab[s - 1][i] >> 8) ^ t->crc_tab[0][t->crc_tab[s - 1][i] & 0xffu];
     t->crc_x2n[0] = 0x40000000u; /* x^1 */
     for (int k = 1; k < 32; k++) t->crc_x2n[k] = crc_gf_mul(t->crc_x2n[k - 1], t->crc_x2n[k - 1]);
+    /* descrambler sequences (decode_impl.cc:304-323): state = first seven received bits, bit i at position 6 - i */
+    for (int st0 = 0; st0 < 128; st0++) {
+        int state = st0;
+        for (int k = 0; k < 160; k++) {
+            int fb = ((state >> 6) & 1) ^ ((state >> 3) & 1);
+            state = ((state << 1) & 0x7e) | fb;
+            t->scr_seq[st0][k >> 5] |= (uint32_t)fb << (k & 31);
+        }
+    }
     t->crc_xpow8[0] = 0x80000000u; /* x^0 */
     for (int n = 1; n < W_XPOW8; n++) t->crc_xpow8[n] = crc_gf_mul(t->crc_x2n[3], t->crc_xpow8[n - 1]);
     /* pilot polarity: scrambler output with the all-ones seed, 0 -> +1, 1 -> -1 (17.3.5.10) */

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 TAB_DTYPE = np.dtype([("pilot_p", "<f4", 128), ("ltf_nl", "<f4", 64), ("sig_demap", "i1", 64), ("bin_j_l", "i1", 64),
                       ("bin_j_nl", "i1", 64), ("sigb_deint", "u1", 52), ("sigb_int", "u1", 52),
-                      ("map", "<u2", (19, 416)), ("crc_tab", "<u4", (4, 256)), ("crc_x2n", "<u4", 32), ("crc_xpow8", "<u4", 4224)], align=True)
+                      ("map", "<u2", (19, 416)), ("crc_tab", "<u4", (4, 256)), ("crc_x2n", "<u4", 32), ("crc_xpow8", "<u4", 4224), ("scr_seq", "<u4", (128, 8))], align=True)
 
 
 @pytest.fixture(scope="module")
@@ -78,6 +78,23 @@ def test_crc_tables_against_zlib(tab):
     frame = rng.integers(0, 256, 90, dtype=np.uint8).tobytes()
     frame += zlib.crc32(frame).to_bytes(4, "little")
     assert crc_words(frame) == 558161692
+
+
+def test_descrambler_sequences(tab):
+    """scr_seq[s] = the first 160 outputs of the x^7+x^4+1 register started from state s, as decode_impl::descramble
+    (decode_impl.cc:304-323) generates them one bit at a time."""
+    for s0 in (0, 1, 93, 127, 64, 0b1011101):
+        state, bits = s0, []
+        for _ in range(160):
+            fb = ((state >> 6) & 1) ^ ((state >> 3) & 1)
+            state = ((state << 1) & 0x7E) | fb
+            bits.append(fb)
+        words = [sum(b << i for i, b in enumerate(bits[32 * w: 32 * w + 32])) for w in range(5)]
+        assert [int(v) for v in tab["scr_seq"][s0][:5]] == words and not tab["scr_seq"][s0][5:].any()
+    # the sequence has period 127 for every non-zero state
+    seq = tab["scr_seq"][93]
+    bit = lambda k: (int(seq[k >> 5]) >> (k & 31)) & 1
+    assert all(bit(k) == bit(k + 127) for k in range(33))
 
 
 def test_library_exports_every_declared_symbol():

@@ -24,7 +24,12 @@ for l in dis.splitlines():
 rows = list(csv.reader(open(src)))
 hdr = rows[1]
 iS, iI, iA = hdr.index("# Samples"), hdr.index("Instructions Executed"), hdr.index("Address")
-body = [r for r in rows[2:] if len(r) > iS]
+body = []
+for r in rows[2:]:
+    if r and r[0] == "Kernel Name":  # a second launch of the kernel in the same export: the first one is enough
+        break
+    if len(r) > iS:
+        body.append(r)
 base = int(body[0][iA], 16)
 tot = sum(float(r[iS] or 0) for r in body)
 toti = sum(float(r[iI] or 0) for r in body)
