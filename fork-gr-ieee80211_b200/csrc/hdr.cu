@@ -24,11 +24,6 @@ struct HdrSmem {
     uint8_t coded[52];
 };
 
-__device__ __forceinline__ float sel4(int l, float v0, float v1, float v2, float v3)
-{
-    return l == 0 ? v0 : (l == 1 ? v1 : (l == 2 ? v2 : v3));
-}
-
 /* svSigDecoder::decode (cloud80211phy.cc:2001-2088): K=7 soft Viterbi over n <= 48 steps with the
  * reference's sentinel / strict '>' / ascending-source-order rules, survivors kept as source state
  * indices, full traceback from state 0.  Lane l owns destinations l and l+32, whose sources are
@@ -42,12 +37,17 @@ __device__ void sig_viterbi(HdrSmem& S, const float* llr, int n, int lane)
     S.surv[0][lane + 32] = 0;
     __syncwarp();
     const int L = w_branch_label(2 * lane, 0);
+    /* the lane's two branch metrics {0, t1, t0, t1+t0}[L] and [3 - L], picked with masks made once: a select on the
+     * lane-dependent label inside the loop compiles to branches, a quarter of this kernel's stall samples */
+    const uint32_t a1 = L == 1 ? ~0u : 0u, a0 = L == 2 ? ~0u : 0u, a3 = L == 3 ? ~0u : 0u;
+    const uint32_t b1 = L == 2 ? ~0u : 0u, b0 = L == 1 ? ~0u : 0u, b3 = L == 0 ? ~0u : 0u;
     int cur = 0;
     for (int t = 0; t < n; t++) {
         float t0 = llr[2 * t], t1 = llr[2 * t + 1];
         float t3 = __fadd_rn(t1, t0);
         float ma = S.met[cur][2 * lane], mb = S.met[cur][2 * lane + 1];
-        float la = sel4(L, 0.0f, t1, t0, t3), lb = sel4(3 - L, 0.0f, t1, t0, t3);
+        const uint32_t u0 = __float_as_uint(t0), u1 = __float_as_uint(t1), u3 = __float_as_uint(t3);
+        float la = __uint_as_float((u1 & a1) | (u0 & a0) | (u3 & a3)), lb = __uint_as_float((u1 & b1) | (u0 & b0) | (u3 & b3));
         /* destination `lane` (input bit 0) */
         float c0 = __fadd_rn(ma, la), c1 = __fadd_rn(mb, lb);
         float best = NEG;
