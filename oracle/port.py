@@ -1,5 +1,5 @@
-"""ctypes front end of oracle/libport80211.so (oracle/port/decode_port.c): the plain-C restatement of the reference's
-decode block.  TEST INFRASTRUCTURE ONLY -- see the header of decode_port.c."""
+"""ctypes front end of oracle/libport80211.so (oracle/port/decode_port.c, demod_port.c): the plain-C restatement of the
+reference's decode block and of its per-symbol demodulation.  TEST INFRASTRUCTURE ONLY -- see the headers of those files."""
 import ctypes as C
 import os
 
@@ -23,6 +23,9 @@ def lib():
         L.port_descramble.argtypes = [vp, vp, ci]
         L.port_trellis_tables.argtypes = [vp, vp]
         L.port_decode_packet.argtypes = [vp, ci, ci, ci, ci, ci, ci, ci, vp, ci, vp, vp]
+        L.port_chan_nl.argtypes = [vp, vp]
+        L.port_chan_nl.restype = None
+        L.port_demod_data.argtypes = [ci, ci, ci, ci, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -65,3 +68,27 @@ def run_decode(packets):
     for p in packets:
         msgs += decode_packet(p)[0]
     return msgs
+
+
+def demod_packet(post, chan_legacy, fmt, nbpscs, nsym, short_gi=False):
+    """One packet's post-L-SIG samples on one antenna (what the signal block hands to demod) -> the LLR stream of its
+    data symbols (demod_port.c).  fmt 0 legacy / 1 HT / 2 VHT; the caller says what the header stage would have found:
+    bits per subcarrier, number of data symbols, short GI.  HT/VHT: the channel comes from the HT/VHT-LTF at sample 240
+    (after HT-SIG / VHT-SIG-A and the STF), data starts after it (HT) or after VHT-SIG-B (demod_impl.cc:120,172,199)."""
+    x = np.ascontiguousarray(post, np.complex64)
+    nsd = 48 if fmt == 0 else 52
+    if fmt == 0:
+        H = np.ascontiguousarray(chan_legacy, np.complex64)
+        base = 0
+    else:
+        H = np.zeros(64, np.complex64)
+        lib().port_chan_nl(x[240:].ctypes.data, H.ctypes.data)
+        base = 320 if fmt == 1 else 400
+    out = np.zeros(nsym * nsd * nbpscs, np.float32)
+    data = x[base:]
+    nss = 72 if short_gi else 80
+    assert len(data) >= nsym * nss
+    r = lib().port_demod_data(fmt, nsym, nss, nbpscs, data.ctypes.data, H.ctypes.data, out.ctypes.data)
+    if r < 0:
+        raise ValueError("port_demod_data: bad parameters")
+    return out

@@ -12,7 +12,8 @@
  *   port_assemble    packetAssemble + boost::crc_32_type   decode_impl.cc:325-520, decode_impl.h:84
  * Pinned by tests/test_port.py against the reference's golden fixture (tests/golden/fixture_*.npz: LLR stream ->
  * the 94-byte frame of tools/debug.txt:5) and against oracle/_ref on random packets of every code rate.
- * The demod half has no plain-C restatement: its checker is oracle/_ref (the reference sources themselves).
+ * The per-symbol demodulation is restated next door, in demod_port.c; the header stage (SIG parsing) is checked by
+ * oracle/_ref only (the reference sources themselves).
  */
 #include <stdint.h>
 #include <stdlib.h>

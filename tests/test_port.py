@@ -1,5 +1,6 @@
-"""The plain-C restatement of the reference's decode block (oracle/port/decode_port.c) against the reference's golden
-fixture and against the reference blocks themselves (oracle/_ref).  CPU only."""
+"""The plain-C restatements of the reference's decode block (oracle/port/decode_port.c) and of its per-symbol
+demodulation (oracle/port/demod_port.c) against the reference's golden fixture and against the reference blocks
+themselves (oracle/_ref).  CPU only."""
 import os
 
 import numpy as np
@@ -49,3 +50,37 @@ def test_port_matches_reference_decode_on_every_code_rate(refgr):
     x = np.random.default_rng(3).normal(0, 1, 2 * 500).astype(np.float32)
     bits, used = port.viterbi(x, 500, 0)
     assert used == 1000 and np.array_equal(bits, refgr.sv_decode(x, 500))
+
+
+def test_demod_port_reproduces_the_reference_fixture():
+    """Samples + legacy channel of tools/sig80211GenMultipleSiso_1x1_0.bin (committed fixture) -> the LLR stream the
+    reference's demod block produced from them, bit for bit (legacy BPSK, 33 symbols)."""
+    z = np.load(os.path.join(GOLD, "fixture_siso.npz"))
+    fmt, mcs, ln, cr, ampdu, trellis, total = [int(x) for x in z["tags"]]
+    assert fmt == 0 and total == 33 * 48
+    llr = port.demod_packet(z["post"][0], z["chan"], 0, 1, total // 48)
+    assert np.array_equal(llr, z["llr"])
+
+
+NB_L = [1, 1, 2, 2, 4, 4, 6, 6]
+NB_NL = [1, 2, 2, 4, 4, 6, 6, 6, 8, 8]
+
+
+@pytest.mark.parametrize("fmt,mcs,length,sgi", [(0, 0, 60, False), (0, 3, 200, False), (0, 5, 333, False), (0, 7, 1500, False),
+                                                (1, 0, 40, False), (1, 2, 300, False), (1, 4, 700, False), (1, 7, 1200, False),
+                                                (1, 7, 900, True), (2, 1, 100, False), (2, 5, 1000, False), (2, 8, 2000, False),
+                                                (2, 8, 1500, True)])
+def test_demod_port_matches_reference_demod(refgr, fmt, mcs, length, sgi):
+    """Generated packets of every modulation, long and short GI: the port's LLRs of the data symbols equal the
+    reference demod block's (oracle/_ref), element for element."""
+    from util import ref_chain
+    f = [g.F_L, g.F_HT, g.F_VHT][fmt]
+    b = gp.gen_batch(f, mcs, 1, length, 3, snr_db=25, short_gi=sgi, seed=900 + 17 * fmt + mcs)
+    ref_pkts, _ = ref_chain(refgr, [b])
+    nb = NB_L[mcs] if fmt == 0 else NB_NL[mcs]
+    nsd = 48 if fmt == 0 else 52
+    for p, r in enumerate(ref_pkts):
+        assert int(r["format"]) == fmt
+        nsym = int(r["total"]) // (nsd * nb)
+        got = port.demod_packet(b["post"][0][p], b["chan"][p], fmt, nb, nsym, short_gi=sgi)
+        assert np.array_equal(got, r["llr"][: len(got)]) and len(got) == int(r["total"])
