@@ -301,3 +301,21 @@ def test_submit_collect_errors_leave_the_slot_usable():
         assert rx2.collect(1).messages() == ok.messages()
     finally:
         rx2.close()
+
+
+@pytest.mark.parametrize("fmt,mcs,length,sgi", [(0, 7, 1500, False), (1, 7, 4095, True), (2, 8, 4088, False), (2, 3, 77, True)])
+def test_llrs_equal_the_plain_c_port(rx, fmt, mcs, length, sgi):
+    """The CUDA demod against the plain-C restatement of the reference's per-symbol demodulation (oracle/port/demod_port.c),
+    which needs neither the reference tree nor its prebuilt blocks: LLRs of full-size packets, element for element."""
+    from oracle import port
+    if not port.available():
+        pytest.skip("oracle/libport80211.so not built")
+    f = [g.F_L, g.F_HT, g.F_VHT][fmt]
+    b = gp.gen_batch(f, mcs, 1, length, 4, snr_db=28, short_gi=sgi, seed=950 + mcs)
+    iq, pk, chan = host.pack_batch([b])
+    res = rx.demod(iq, pk, chan)
+    for p in range(len(pk)):
+        d = res.desc[p]
+        assert int(d["status"]) == host.ST_OK and int(d["format"]) == fmt
+        want = port.demod_packet(b["post"][0][p], b["chan"][p], fmt, int(d["nbpscs"]), int(d["nsym"]), short_gi=sgi)
+        assert np.array_equal(res.packet_llr(p), want)
