@@ -18,7 +18,6 @@ struct HdrSmem {
     float2 eq[2][64];    /* equalised bins (d_sig1 / d_sig2 of the reference) */
     float2 qam[2][52];   /* VHT-SIG-B symbols after phase correction */
     float llr[2][96];    /* [0] HT hypothesis, [1] VHT hypothesis; reused for SIG-B */
-    float met[2][64];
     uint8_t surv[49][64];
     uint8_t bits[48];
     uint8_t coded[52];
@@ -31,21 +30,26 @@ struct HdrSmem {
 __device__ void sig_viterbi(HdrSmem& S, const float* llr, int n, int lane)
 {
     const float NEG = -1000000000000000.0f;
-    S.met[0][lane] = lane == 0 ? 0.0f : NEG;
-    S.met[0][lane + 32] = NEG;
+    /* Path metrics stay in registers: lane l owns states l (lo) and l + 32 (hi) and fetches its two sources 2l, 2l + 1
+     * with shuffles (lanes (2l) & 31 and (2l + 1) & 31; their lo half when l < 16, else their hi half) -- no shared-memory
+     * round trip and no warp barrier per step. */
+    float lo = lane == 0 ? 0.0f : NEG, hi = NEG;
     S.surv[0][lane] = 0;
     S.surv[0][lane + 32] = 0;
-    __syncwarp();
     const int L = w_branch_label(2 * lane, 0);
     /* the lane's two branch metrics {0, t1, t0, t1+t0}[L] and [3 - L], picked with masks made once: a select on the
      * lane-dependent label inside the loop compiles to branches, a quarter of this kernel's stall samples */
     const uint32_t a1 = L == 1 ? ~0u : 0u, a0 = L == 2 ? ~0u : 0u, a3 = L == 3 ? ~0u : 0u;
     const uint32_t b1 = L == 2 ? ~0u : 0u, b0 = L == 1 ? ~0u : 0u, b3 = L == 0 ? ~0u : 0u;
-    int cur = 0;
+    const int sa = (2 * lane) & 31, sb = (2 * lane + 1) & 31;
+    const bool low = lane < 16;
+    __syncwarp(); /* the LLRs were written by other lanes */
     for (int t = 0; t < n; t++) {
         float t0 = llr[2 * t], t1 = llr[2 * t + 1];
         float t3 = __fadd_rn(t1, t0);
-        float ma = S.met[cur][2 * lane], mb = S.met[cur][2 * lane + 1];
+        const float alo = __shfl_sync(0xffffffffu, lo, sa), ahi = __shfl_sync(0xffffffffu, hi, sa);
+        const float blo = __shfl_sync(0xffffffffu, lo, sb), bhi = __shfl_sync(0xffffffffu, hi, sb);
+        float ma = low ? alo : ahi, mb = low ? blo : bhi;
         const uint32_t u0 = __float_as_uint(t0), u1 = __float_as_uint(t1), u3 = __float_as_uint(t3);
         float la = __uint_as_float((u1 & a1) | (u0 & a0) | (u3 & a3)), lb = __uint_as_float((u1 & b1) | (u0 & b0) | (u3 & b3));
         /* destination `lane` (input bit 0) */
@@ -54,7 +58,7 @@ __device__ void sig_viterbi(HdrSmem& S, const float* llr, int n, int lane)
         int sv = 0;
         if (c0 > best) { best = c0; sv = 2 * lane; }
         if (c1 > best) { best = c1; sv = 2 * lane + 1; }
-        S.met[cur ^ 1][lane] = best;
+        lo = best;
         S.surv[t + 1][lane] = (uint8_t)sv;
         /* destination lane+32 (input bit 1): labels swap */
         c0 = __fadd_rn(ma, lb);
@@ -63,11 +67,10 @@ __device__ void sig_viterbi(HdrSmem& S, const float* llr, int n, int lane)
         sv = 0;
         if (c0 > best) { best = c0; sv = 2 * lane; }
         if (c1 > best) { best = c1; sv = 2 * lane + 1; }
-        S.met[cur ^ 1][lane + 32] = best;
+        hi = best;
         S.surv[t + 1][lane + 32] = (uint8_t)sv;
-        cur ^= 1;
-        __syncwarp();
     }
+    __syncwarp();
     if (lane == 0) {
         int st = 0;
         for (int j = n; j > 0; j--) {
