@@ -28,9 +28,6 @@
 #ifndef VIT_INPLACE
 #define VIT_INPLACE 1
 #endif
-#ifndef VIT_REGPF
-#define VIT_REGPF 1 /* 1: software-pipelined register prefetch of the next body's LLRs */
-#endif
 #ifndef VIT_PF
 #define VIT_PF 8 /* L1 prefetch distance, in bodies */
 #endif
@@ -148,18 +145,22 @@ __device__ __forceinline__ void acs2_ip(float (&m)[64], float a0, float a1, floa
     *dst = w;
 }
 
-/* six steps, rates 1/2 (12 LLRs) and 3/4 (8 LLRs) */
+/* six steps, rates 1/2 (12 LLRs), 3/4 (8 LLRs) and 2/3 (9 LLRs: three periods of {1,1},{1,0}) */
 template <int CR>
-__device__ __forceinline__ void body6(float (&m)[64], const float4* v, uint4* dst)
+__device__ __forceinline__ void body6(float (&m)[64], const float* v, uint4* dst)
 {
     if (CR == W80211_CR_12) {
-        acs2_ip<0, MASK_FULL, MASK_FULL>(m, v[0].x, v[0].y, v[0].z, v[0].w, dst);
-        acs2_ip<2, MASK_FULL, MASK_FULL>(m, v[1].x, v[1].y, v[1].z, v[1].w, dst + 32);
-        acs2_ip<4, MASK_FULL, MASK_FULL>(m, v[2].x, v[2].y, v[2].z, v[2].w, dst + 64);
+        acs2_ip<0, MASK_FULL, MASK_FULL>(m, v[0], v[1], v[2], v[3], dst);
+        acs2_ip<2, MASK_FULL, MASK_FULL>(m, v[4], v[5], v[6], v[7], dst + 32);
+        acs2_ip<4, MASK_FULL, MASK_FULL>(m, v[8], v[9], v[10], v[11], dst + 64);
+    } else if (CR == W80211_CR_23) {
+        acs2_ip<0, MASK_FULL, MASK_A>(m, v[0], v[1], v[2], 0.f, dst);
+        acs2_ip<2, MASK_FULL, MASK_A>(m, v[3], v[4], v[5], 0.f, dst + 32);
+        acs2_ip<4, MASK_FULL, MASK_A>(m, v[6], v[7], v[8], 0.f, dst + 64);
     } else {
-        acs2_ip<0, MASK_FULL, MASK_A>(m, v[0].x, v[0].y, v[0].z, 0.f, dst);
-        acs2_ip<2, MASK_B, MASK_FULL>(m, 0.f, v[0].w, v[1].x, v[1].y, dst + 32);
-        acs2_ip<4, MASK_A, MASK_B>(m, v[1].z, 0.f, 0.f, v[1].w, dst + 64);
+        acs2_ip<0, MASK_FULL, MASK_A>(m, v[0], v[1], v[2], 0.f, dst);
+        acs2_ip<2, MASK_B, MASK_FULL>(m, 0.f, v[3], v[4], v[5], dst + 32);
+        acs2_ip<4, MASK_A, MASK_B>(m, v[6], 0.f, 0.f, v[7], dst + 64);
     }
 }
 
@@ -179,43 +180,59 @@ __device__ __forceinline__ void tail_ip(float (&m)[64], int& t, int trellis, int
     }
 }
 
+/* floats of one six-step body; rates 1/2 and 3/4 read them as aligned float4, rate 2/3 (9 floats) as scalars */
+template <int CR> struct Body6 { enum { NF = CR == W80211_CR_12 ? 12 : (CR == W80211_CR_23 ? 9 : 8) }; };
+
+template <int CR>
+__device__ __forceinline__ void load_body6(const float* __restrict__ llr, int b, float* v)
+{
+    enum { NF = Body6<CR>::NF };
+    if (NF % 4 == 0) {
+        const float4* src = reinterpret_cast<const float4*>(llr) + (size_t)b * (NF / 4);
+#pragma unroll
+        for (int k = 0; k < NF / 4; k++) {
+            const float4 x = __ldg(src + k);
+            v[4 * k] = x.x;
+            v[4 * k + 1] = x.y;
+            v[4 * k + 2] = x.z;
+            v[4 * k + 3] = x.w;
+        }
+    } else {
+        const float* src = llr + (size_t)b * NF;
+#pragma unroll
+        for (int k = 0; k < NF; k++) v[k] = __ldg(src + k);
+    }
+}
+
 template <int CR>
 __device__ __forceinline__ void viterbi_run6(const float* __restrict__ llr, int trellis, uint4* __restrict__ surv4)
 {
-    enum { NV = CR == W80211_CR_12 ? 3 : 2 };
+    enum { NF = Body6<CR>::NF };
     const float NEG = -1000000000000000.0f;
     float m[64];
 #pragma unroll
     for (int i = 0; i < 64; i++) m[i] = NEG;
     m[0] = 0.0f;
     const int nbody = trellis / 6;
-    const float4* src = reinterpret_cast<const float4*>(llr);
-#if VIT_REGPF
     /* next body's LLRs are loaded into registers while the current body computes; L2 prefetch further ahead */
-    float4 cur[NV], nxt[NV];
+    float cur[NF], nxt[NF];
+    if (nbody > 0) {
+        load_body6<CR>(llr, 0, cur);
+    } else {
 #pragma unroll
-    for (int k = 0; k < NV; k++) cur[k] = nbody > 0 ? __ldg(src + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < NF; k++) cur[k] = 0.f;
+    }
     for (int b = 0; b < nbody; b++) {
         const int bn = b + 1 < nbody ? b + 1 : b;
-#pragma unroll
-        for (int k = 0; k < NV; k++) nxt[k] = __ldg(src + (size_t)bn * NV + k);
-        if (b + VIT_PF < nbody) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(b + VIT_PF) * NV));
+        load_body6<CR>(llr, bn, nxt);
+        if (b + VIT_PF < nbody) asm volatile("prefetch.global.L2 [%0];" ::"l"(llr + (size_t)(b + VIT_PF) * NF));
         body6<CR>(m, cur, surv4 + (size_t)b * 3 * 32);
 #pragma unroll
-        for (int k = 0; k < NV; k++) cur[k] = nxt[k];
+        for (int k = 0; k < NF; k++) cur[k] = nxt[k];
     }
-#else
-    for (int b = 0; b < nbody; b++) {
-        float4 cur[NV];
-#pragma unroll
-        for (int k = 0; k < NV; k++) cur[k] = __ldg(src + (size_t)b * NV + k);
-        if (b + VIT_PF < nbody) asm volatile("prefetch.global.L1 [%0];" ::"l"(src + (size_t)(b + VIT_PF) * NV));
-        body6<CR>(m, cur, surv4 + (size_t)b * 3 * 32);
-    }
-#endif
     int t = nbody * 6, ph = 0;
-    const int period = CR == W80211_CR_12 ? 1 : 3;
-    const float* q = llr + (size_t)nbody * NV * 4;
+    const int period = CR == W80211_CR_12 ? 1 : (CR == W80211_CR_23 ? 2 : 3);
+    const float* q = llr + (size_t)nbody * NF;
     uint2* surv2 = reinterpret_cast<uint2*>(surv4);
     tail_ip<0>(m, t, trellis, ph, period, q, surv2);
     tail_ip<1>(m, t, trellis, ph, period, q, surv2);
@@ -290,7 +307,7 @@ __global__ void __launch_bounds__(32, VIT_MINBLK) viterbi_kernel(const int4* __r
     const float* l = llr + desc[pkt].llr_off;
     uint4* s4 = reinterpret_cast<uint4*>(surv + (size_t)G.x * 32) + lane;
 #if VIT_INPLACE
-    if (CR == W80211_CR_12 || CR == W80211_CR_34)
+    if (CR == W80211_CR_12 || CR == W80211_CR_34 || CR == W80211_CR_23)
         viterbi_run6<CR>(l, trellis, s4);
     else
 #endif
