@@ -34,9 +34,16 @@ MPDU_LEN = 4088
 N_UNIQUE = 512
 
 
+CONFIG = "C4"  # --config: the other single-antenna configurations of BASELINE.json, for tuning runs only
+
+
 def gen_unique(n, seed):
     import w80211rx
     gp, g = w80211rx.gen_ppdu, w80211rx.gen
+    if CONFIG == "C2":  # legacy 54 Mb/s, 1500 B
+        return gp.gen_batch(g.F_L, 7, 1, 1500, n, snr_db=30, seed=seed)
+    if CONFIG == "C3":  # HT MCS7 short GI, 4095 B (rate 5/6, trellis 32782)
+        return gp.gen_batch(g.F_HT, 7, 1, 4095, n, snr_db=30, short_gi=True, seed=seed)
     return gp.gen_batch(g.F_VHT, 8, 1, MPDU_LEN, n, snr_db=30, seed=seed)
 
 
@@ -352,7 +359,7 @@ def main_gpu(args):
     t_to = clocks.mark()
     launches = counters["launches"] * args.steps // KSEQ
     if args.resident_only:
-        print(json.dumps({"value": bits / (ms * 1e-3) / 1e9, "ms_per_step": ms / args.steps, "packets": P, "lib": os.environ.get("W80211_LIB"),
+        print(json.dumps({"config": CONFIG, "value": bits / (ms * 1e-3) / 1e9, "ms_per_step": ms / args.steps, "packets": P, "lib": os.environ.get("W80211_LIB"),
                           "fcs_ok_per_step": npk_ok / args.steps, "clocks": clocks.stop(t_from, t_to),
                           "stage_ms_per_step": {k: round(v / KSEQ, 4) for k, v in stage.items()}}))
         rx.close()
@@ -582,10 +589,14 @@ def main():
     ap.add_argument("--mpdu-len", type=int, default=4088, help="profiling only: shorter packets; the reported workload is the default")
     ap.add_argument("--ref-packets", type=int, default=512, help="packets per core and step for the CPU reference")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--config", default="C4", choices=["C2", "C3", "C4"], help="tuning runs (with --resident-only): another single-antenna configuration of BASELINE.json; the benchmark workload is C4")
     ap.add_argument("--resident-only", action="store_true", help="tuning runs: the resident leg and the per-kernel times only, short JSON line")
     args = ap.parse_args()
-    global MPDU_LEN
+    global MPDU_LEN, CONFIG
     MPDU_LEN = args.mpdu_len
+    CONFIG = args.config
+    if CONFIG != "C4" and not args.resident_only and args.impl == "ours":
+        ap.error("--config other than C4 is for --resident-only tuning runs")
     if args.impl == "reference":
         return main_reference(args)
     return main_gpu(args)
