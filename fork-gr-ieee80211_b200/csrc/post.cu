@@ -15,7 +15,9 @@
  */
 #include "common.cuh"
 
-#define POST_WARPS 4
+#ifndef POST_WARPS
+#define POST_WARPS 8 /* one CRC table copy per 8 packets; 37 KB of static shared memory, 6 blocks per SM */
+#endif
 #define POST_MAXW 1028 /* ceil(32782/32) = 1025 words, padded */
 #define CRC_POLY 0xEDB88320u
 #define CRC_RESIDUE 558161692u
