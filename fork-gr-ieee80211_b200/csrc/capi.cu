@@ -69,7 +69,9 @@ struct Slot {
     size_t plan_o_psdu = 0; /* offset of the psdu_off array inside h_plan */
     bool did_demod = false, did_decode = false, in_host = true;
     uint64_t n_llr = 0, n_bytes = 0, trellis_steps = 0;
-    uint32_t mpdu_cap = 0;
+    uint32_t mpdu_cap = 0;   /* records the device / pinned buffers of this batch can hold */
+    uint32_t mpdu_eager = 0; /* records copied to the host together with the counters */
+    uint8_t* post_bytes = nullptr; /* where the post kernel writes PSDU bytes (the caller's device buffer or s.bytes) */
     uint32_t launches = 0;
     w80211_batch_out* out = nullptr;
     std::vector<uint32_t> h_psdu_off;
@@ -97,6 +99,8 @@ struct SigStage {
 struct w80211_ctx {
     int device = 0;
     int nslots = 2;
+    int vit_mode = W80211_CFG_VITERBI_AUTO; /* w80211_cfg.flags & W80211_CFG_VITERBI_MASK */
+    int warp_max_pkts = 7168;               /* AUTO: a code rate with fewer packets than this in a batch takes the warp-per-packet kernels */
     cudaEvent_t origin = nullptr;    /* W80211_TRACE=1: time zero of the per-batch timelines printed by collect_slot */
     std::deque<int> pending;         /* slots in phase 1, in submission order */
     /* The input copies of all slots go through this one stream, so they reach the device one batch after the other at the
@@ -323,17 +327,23 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
     cudaStream_t st = s.stream;
     w80211_batch_out* out = s.out;
     CK(cudaEventRecord(s.ev[EV_VIT0], st));
+    int warp_mask = 0;
+    for (int cr = 0; cr < 4; cr++) {
+        const int npk = (s.cr_first[cr + 1] - s.cr_first[cr]) * 32;
+        if (ctx->vit_mode == W80211_CFG_VITERBI_WARP || (ctx->vit_mode == W80211_CFG_VITERBI_AUTO && npk < ctx->warp_max_pkts)) warp_mask |= 1 << cr;
+    }
     int nvit = w_launch_viterbi(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
-                                (const float*)s.llr.p, (uint2*)s.surv.p);
+                                (const float*)s.llr.p, (uint2*)s.surv.p, warp_mask);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_VIT], st));
-    w_launch_traceback(st, s.ngroups, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
-                       (const uint2*)s.surv.p, (uint32_t*)s.bits.p);
+    nvit += w_launch_traceback(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
+                               (const uint2*)s.surv.p, (uint32_t*)s.bits.p, warp_mask);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_TB], st));
-    /* MPDU record capacity: one per packet is the rule; VHT A-MPDUs can hold more */
-    s.mpdu_cap = out->mpdus ? out->mpdu_capacity : 0;
-    uint32_t internal_cap = (uint32_t)std::max<size_t>((size_t)s.ndec * 2 + 64, s.mpdu_cap);
+    /* MPDU records: one per packet is the rule, a VHT A-MPDU has one per delimiter walked (up to trellis / 32 + 1).  The
+     * buffers start at 1.5 per packet; a batch that produces more is finished by collect_slot(), which knows the exact
+     * count by then, grows the buffers and runs the post kernel once more (launch_post_again). */
+    uint32_t internal_cap = (uint32_t)std::min<size_t>((size_t)s.ndec + (size_t)s.ndec / 2 + 64, 0xffffffffu);
     RS(dev_reserve(ctx, s.mpdus, (size_t)internal_cap * sizeof(w80211_mpdu)));
     RS(pin_reserve(ctx, s.h_mpdus, (size_t)internal_cap * sizeof(w80211_mpdu)));
     RS(pin_reserve(ctx, s.h_counters, 64));
@@ -345,16 +355,19 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
     if (out->bytes && out->bytes_capacity < s.n_bytes)
         return fail(ctx, W80211_E_CAPACITY, "bytes_capacity %llu < %llu needed", (unsigned long long)out->bytes_capacity,
                     (unsigned long long)s.n_bytes);
+    s.post_bytes = bytes_in_place ? out->bytes : (uint8_t*)s.bytes.p;
     w_launch_post(st, ctx->d_tab, s.ndec, (const int4*)s.grp.p, (const int*)s.pkt_slot.p, (const int*)s.dec_list.p,
-                  (const w80211_desc*)s.desc.p, (const uint32_t*)s.bits.p, (const uint32_t*)s.psdu_off.p,
-                  bytes_in_place ? out->bytes : (uint8_t*)s.bytes.p, (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
+                  (const w80211_desc*)s.desc.p, (const uint32_t*)s.bits.p, (const uint32_t*)s.psdu_off.p, s.post_bytes,
+                  (w80211_mpdu*)s.mpdus.p, internal_cap, (unsigned int*)s.counters.p);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_POST], st));
     ctx->last_tail = s.ev[EV_POST];
-    if (s.ngroups > 0) s.launches += 2 + nvit;
-    /* results */
+    if (s.ngroups > 0) s.launches += 1 + nvit;
+    /* results: the counters and one record per packet now, the rest (A-MPDUs with several subframes) when collect_slot()
+     * has read the count */
+    s.mpdu_eager = (uint32_t)std::min<size_t>((size_t)s.ndec + 64, internal_cap);
     CK(cudaMemcpyAsync(s.h_counters.p, s.counters.p, 64, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(s.h_mpdus.p, s.mpdus.p, (size_t)internal_cap * sizeof(w80211_mpdu), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(s.h_mpdus.p, s.mpdus.p, (size_t)s.mpdu_eager * sizeof(w80211_mpdu), cudaMemcpyDeviceToHost, st));
     if (out->bytes && !bytes_in_place && s.n_bytes)
         CK(cudaMemcpyAsync(out->bytes, s.bytes.p, s.n_bytes,
                            out->mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
@@ -516,6 +529,27 @@ int continue_front(w80211_ctx* ctx, Slot& s)
     return 0;
 }
 
+/* The post kernel counted `need` MPDU records but could store only s.mpdu_cap of them: grow the buffers to the exact
+ * count and run it again (its inputs are still in the slot's buffers; it rewrites the same bytes). */
+int launch_post_again(w80211_ctx* ctx, Slot& s, uint32_t need)
+{
+    cudaStream_t st = s.stream;
+    RS(dev_reserve(ctx, s.mpdus, (size_t)need * sizeof(w80211_mpdu)));
+    RS(pin_reserve(ctx, s.h_mpdus, (size_t)need * sizeof(w80211_mpdu)));
+    s.mpdu_cap = need;
+    CK(cudaMemsetAsync(s.counters.p, 0, 64, st));
+    w_launch_post(st, ctx->d_tab, s.ndec, (const int4*)s.grp.p, (const int*)s.pkt_slot.p, (const int*)s.dec_list.p,
+                  (const w80211_desc*)s.desc.p, (const uint32_t*)s.bits.p, (const uint32_t*)s.psdu_off.p, s.post_bytes,
+                  (w80211_mpdu*)s.mpdus.p, need, (unsigned int*)s.counters.p);
+    CK(cudaGetLastError());
+    s.launches += 1;
+    CK(cudaMemcpyAsync(s.h_counters.p, s.counters.p, 64, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(s.h_mpdus.p, s.mpdus.p, (size_t)need * sizeof(w80211_mpdu), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (((const unsigned int*)s.h_counters.p)[0] != need) return fail(ctx, W80211_E_STATE, "MPDU record count changed between two runs of the post kernel");
+    return 0;
+}
+
 int collect_slot(w80211_ctx* ctx, Slot& s)
 {
     if (!s.busy) return fail(ctx, W80211_E_STATE, "slot idle: nothing to collect");
@@ -543,7 +577,14 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
     if (s.did_decode) {
         const unsigned int* c = (const unsigned int*)s.h_counters.p;
         uint32_t n = c[0];
-        if (n > s.mpdu_cap) return fail(ctx, W80211_E_CAPACITY, "MPDU records overflow: %u > %u", n, s.mpdu_cap);
+        if (n > s.mpdu_cap) RS(launch_post_again(ctx, s, n)); /* more subframes than the buffers held: now the count is known */
+        else if (n > s.mpdu_eager) {
+            CK(cudaMemcpyAsync((w80211_mpdu*)s.h_mpdus.p + s.mpdu_eager, (const w80211_mpdu*)s.mpdus.p + s.mpdu_eager,
+                               (size_t)(n - s.mpdu_eager) * sizeof(w80211_mpdu), cudaMemcpyDeviceToHost, s.stream));
+            CK(cudaStreamSynchronize(s.stream));
+        }
+        c = (const unsigned int*)s.h_counters.p;
+        n = c[0];
         w80211_mpdu* hm = (w80211_mpdu*)s.h_mpdus.p;
         /* records arrive in completion order; put them in (pkt, off) order with one counting pass over the packets */
         auto rec_before = [](const w80211_mpdu& a, const w80211_mpdu& b) { return a.pkt != b.pkt ? a.pkt < b.pkt : a.off < b.off; };
@@ -698,6 +739,8 @@ int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
     if (!ctx) return W80211_E_NOMEM;
     ctx->device = cfg ? cfg->device : 0;
     ctx->nslots = cfg && cfg->nslots > 0 ? std::min(cfg->nslots, 4) : 2;
+    ctx->vit_mode = cfg ? (cfg->flags & W80211_CFG_VITERBI_MASK) : W80211_CFG_VITERBI_AUTO;
+    if (const char* e = getenv("W80211_WARP_MAX_PKTS")) ctx->warp_max_pkts = atoi(e);
     if (ctx->device < 0 || ctx->device >= ndev || cudaSetDevice(ctx->device) != cudaSuccess) {
         delete ctx;
         return W80211_E_ARG;
@@ -707,6 +750,7 @@ int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
     bool ok = cudaMalloc(&ctx->d_tab, sizeof(W80211Tables)) == cudaSuccess &&
               cudaMemcpy(ctx->d_tab, ht, sizeof(W80211Tables), cudaMemcpyHostToDevice) == cudaSuccess;
     delete ht;
+    ok = ok && w_demod_init_device() == 0;
     ok = ok && cudaStreamCreateWithFlags(&ctx->cstream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < ctx->nslots; i++) {
         ok = cudaStreamCreateWithFlags(&ctx->slots[i].stream, cudaStreamNonBlocking) == cudaSuccess;

@@ -182,6 +182,7 @@ __host__ __device__ constexpr int w_branch_label(int st, int b)
 void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nant, const float2* iq0, const float2* iq1,
                      unsigned long long nsamples, const w80211_pkt_in* pk, const float2* chan_in, w80211_desc* desc,
                      float2* chan_out, int chan_stride, int mu_pos);
+int w_demod_init_device(); /* per-device kernel attributes, called by w80211_create() with the context's device current */
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nsymtot, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* sym_prefix,
                     const float2* chan, int chan_stride, float* llr);
@@ -224,9 +225,9 @@ void w_launch_sc16_to_fc32(cudaStream_t st, int npkt, int nant, const w80211_pkt
                            float2* out0, float2* out1, unsigned long long nsamples, int bytes_per_sample);
 void w_launch_upload(cudaStream_t st, void* dst, const void* pinned_src, size_t bytes);
 int w_launch_viterbi(cudaStream_t st, const int* cr_first, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
-                     const float* llr, uint2* surv);
-void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
-                        const uint2* surv, uint32_t* bits);
+                     const float* llr, uint2* surv, int warp_mask);
+int w_launch_traceback(cudaStream_t st, const int* cr_first, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
+                       const uint2* surv, uint32_t* bits, int warp_mask);
 void w_launch_post(cudaStream_t st, const W80211Tables* tab, int npkt_dec, const int4* grp, const int* pkt_slot, const int* dec_list,
                    const w80211_desc* desc, const uint32_t* bits, const uint32_t* psdu_off, uint8_t* out_bytes,
                    w80211_mpdu* mpdus, unsigned int mpdu_cap, unsigned int* counters);

@@ -431,18 +431,21 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     }
 }
 
+/* Function attributes are per device: w80211_create() calls this once for the context's device (the current one). */
+int w_demod_init_device()
+{
+    cudaError_t e = cudaFuncSetAttribute(demod_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<true>));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(demod_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<false>));
+    return e == cudaSuccess ? 0 : -1;
+}
+
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nitems, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* item_prefix,
                     const float2* chan, int chan_stride, float* llr)
 {
     if (nitems <= 0) return;
     int blocks = (nitems + DEMOD_GROUPS - 1) / DEMOD_GROUPS;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(demod_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<true>));
-        cudaFuncSetAttribute(demod_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<false>));
-        attr_set = true;
-    }
     if (nant == 2)
         demod_kernel<true><<<blocks, DEMOD_THREADS, sizeof(DemodSmem<true>), st>>>(tab, nitems, npkt, nant, iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
     else

@@ -320,9 +320,9 @@ __global__ void __launch_bounds__(32, VIT_MINBLK) viterbi_kernel(const int4* __r
  * 32 one-warp blocks fit on an SM and a two-wave Viterbi batch is a single traceback wave. */
 __global__ void __launch_bounds__(32, 32) traceback_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
                                                            const w80211_desc* __restrict__ desc, const uint2* __restrict__ surv,
-                                                           uint32_t* __restrict__ bits)
+                                                           uint32_t* __restrict__ bits, int g0)
 {
-    const int g = blockIdx.x, lane = threadIdx.x;
+    const int g = g0 + blockIdx.x, lane = threadIdx.x;
     const int4 G = grp[g];
     const int pkt = slot_pkt[g * 32 + lane];
     if (pkt < 0) return;
@@ -360,27 +360,391 @@ __global__ void __launch_bounds__(32, 32) traceback_kernel(const int4* __restric
     }
 }
 
+/* =====================================================================================================
+ * Warp-per-packet variant, for launches that cannot fill the machine with one packet per lane.
+ *
+ * Same arithmetic per destination state as above (two FP32 candidate sums, strict '>' with the even
+ * source first, max), so decisions and metrics are the reference's bit for bit; what changes is where
+ * the 64 path metrics live: two per lane.  The state <-> (lane, register) map is not fixed: a
+ * butterfly reads sources (2b, 2b+1) and writes (b, b+32) back into the two registers it read, and
+ * before each step one __shfl_xor over lane bit j swaps one register between partner lanes so that
+ * both sources of a butterfly sit in one lane.  j cycles 4,0,1,2,3 with the step number (t mod 5):
+ *
+ *     phase ph = t mod 5,  j = (ph + 4) mod 5,  lane holds butterfly b = rotr5(lane, ph)
+ *     lanes with bit j clear hold even sources, their partners (bit j set) odd sources;
+ *     send = bit j ? x0 : x1, after the exchange (ma, mb) = bit j ? (recv, x1) : (x0, recv);
+ *     x0 <- max over sources for destination b, x1 <- for destination b + 32.
+ *
+ * State 0 is lane 0 / x0 in every phase, so the initial metrics need no special case.
+ * Survivors: one uint2 per step and packet, (ballot of "odd source won" for x0, for x1) in LANE order
+ * of that step; the traceback below walks (lane, register) positions, not state numbers, so the
+ * permutation never has to be undone:
+ *     decoded bit = r;  dec = bit `lane` of word r;  r' = bit j of lane;  lane' = lane with bit j := dec.
+ * Layout: a group's survivor region (G.y rows of 32 uint2, as for the kernel above) is split into 32
+ * contiguous runs of G.y uint2, one per packet.
+ * ===================================================================================================== */
+#define WV_FULL 0xffffffffu
+__device__ __forceinline__ float bsel(uint32_t m, float a, float b) /* m ? a : b, m all ones or zero: one LOP3 */
+{
+    return __uint_as_float((__float_as_uint(a) & m) | (__float_as_uint(b) & ~m));
+}
+
+struct WvLane {
+    uint32_t up[5]; /* all ones when this lane has bit j(ph) set */
+    /* label L of the lane's butterfly (2b --0--> b) as 0.0f / 1.0f factors: fA = bit A of L (the branch uses t0), fB = bit B
+     * (uses t1); gA, gB the same for the complementary label 3 - L */
+    float fA[5], fB[5], gA[5], gB[5];
+};
+
+__device__ __forceinline__ void wv_setup(int lane, WvLane& W)
+{
+#pragma unroll
+    for (int ph = 0; ph < 5; ph++) {
+        const int j = (ph + 4) % 5;
+        const int b = ((lane >> ph) | (lane << (5 - ph))) & 31; /* rotr5(lane, ph) */
+        const int L = w_branch_label(2 * b, 0);
+        W.up[ph] = (lane >> j) & 1 ? 0xffffffffu : 0u;
+        W.fA[ph] = (L & 2) ? 1.0f : 0.0f;
+        W.fB[ph] = (L & 1) ? 1.0f : 0.0f;
+        W.gA[ph] = (L & 2) ? 0.0f : 1.0f;
+        W.gB[ph] = (L & 1) ? 0.0f : 1.0f;
+        /* opaque to the compiler, or it turns the selects below into ISETP + SEL / FSEL chains (it runs out of predicate
+         * registers and re-derives them every step) */
+        asm volatile("" : "+r"(W.up[ph]), "+f"(W.fA[ph]), "+f"(W.fB[ph]), "+f"(W.gA[ph]), "+f"(W.gB[ph]));
+    }
+}
+
+/* Issue cost on B200 (profiles/r1_pipebench.txt): LOP3 / SEL / FSETP take two cycles of a scheduler's ALU pipe, FADD / FMUL /
+ * FFMA / FMNMX one.  So the branch metrics are picked with exact multiplications by 0.0f / 1.0f on the FMA pipe
+ * (t * 1 = t, t * 0 = +-0, and m + (+-0) = m for every metric m: the sums are the reference's bit for bit as long as the
+ * LLRs are finite), and both registers are shuffled so that only the two receive-side selects remain. */
+template <int PH, int MASK>
+__device__ __forceinline__ uint2 wv_step(float& x0, float& x1, float t0, float t1, const WvLane& W)
+{
+    constexpr int J = (PH + 4) % 5;
+    const uint32_t up = W.up[PH];
+    const float r0 = __shfl_xor_sync(WV_FULL, x0, 1 << J);
+    const float r1 = __shfl_xor_sync(WV_FULL, x1, 1 << J);
+    const float ma = bsel(up, r1, x0); /* even source 2b */
+    const float mb = bsel(up, x1, r0); /* odd source 2b+1 */
+    /* branch metrics {0, t1, t0, t1+t0}[label] (decode_impl.cc:231-234): label L on 2b->b and 2b+1->b+32, 3-L on the other two */
+    float bl, bc;
+    if (MASK == MASK_FULL) {
+        bl = __fmaf_rn(t0, W.fA[PH], __fmul_rn(t1, W.fB[PH]));
+        bc = __fmaf_rn(t0, W.gA[PH], __fmul_rn(t1, W.gB[PH]));
+    } else if (MASK == MASK_A) {
+        bl = __fmul_rn(t0, W.fA[PH]);
+        bc = __fmul_rn(t0, W.gA[PH]);
+    } else {
+        bl = __fmul_rn(t1, W.fB[PH]);
+        bc = __fmul_rn(t1, W.gB[PH]);
+    }
+    const float c0 = __fadd_rn(ma, bl), c1 = __fadd_rn(mb, bc);
+    const float e0 = __fadd_rn(ma, bc), e1 = __fadd_rn(mb, bl);
+    x0 = fmaxf(c0, c1);
+    x1 = fmaxf(e0, e1);
+    uint2 w;
+    w.x = __ballot_sync(WV_FULL, c1 > c0);
+    w.y = __ballot_sync(WV_FULL, e1 > e0);
+    return w;
+}
+
+/* steps per unrolled body (a multiple of 5 and of the puncturing period) and the LLRs it consumes */
+template <int CR> struct WvBody;
+template <> struct WvBody<W80211_CR_12> { enum { STEPS = 10, NF = 20, VW = 4 }; };
+template <> struct WvBody<W80211_CR_23> { enum { STEPS = 20, NF = 30, VW = 2 }; };
+template <> struct WvBody<W80211_CR_34> { enum { STEPS = 15, NF = 20, VW = 4 }; };
+template <> struct WvBody<W80211_CR_56> { enum { STEPS = 10, NF = 12, VW = 4 }; };
+
+/* puncturing (decode_impl.cc:197-229, SV_PUNC_* cloud80211phy.cc:1857-1860): which LLRs step k of a period has */
+template <int CR> __host__ __device__ constexpr int wv_period() { return CR == W80211_CR_12 ? 1 : (CR == W80211_CR_23 ? 2 : (CR == W80211_CR_34 ? 3 : 5)); }
+__host__ __device__ constexpr int wv_mask_of(int k) { return k == 0 ? MASK_FULL : ((k & 1) ? MASK_A : MASK_B); }
+__host__ __device__ constexpr int wv_llrs_before(int k) { return k == 0 ? 0 : k + 1; } /* phase 0 takes two, every later phase one */
+
+template <int CR, int K>
+__device__ __forceinline__ void wv_body_step(float& x0, float& x1, const float* v, const WvLane& W, uint2* dst, bool store)
+{
+    constexpr int PER = wv_period<CR>();
+    constexpr int ph = K % PER, MASK = wv_mask_of(ph);
+    constexpr int base = (K / PER) * (PER + 1) + wv_llrs_before(ph);
+    const float t0 = MASK == MASK_B ? 0.f : v[base];
+    const float t1 = MASK == MASK_A ? 0.f : v[MASK == MASK_FULL ? base + 1 : base];
+    const uint2 w = wv_step<K % 5, MASK>(x0, x1, t0, t1, W);
+    if (store) dst[K] = w;
+}
+
+template <int CR, int K0, int N>
+struct WvUnroll {
+    static __device__ __forceinline__ void run(float& x0, float& x1, const float* v, const WvLane& W, uint2* dst, bool store)
+    {
+        wv_body_step<CR, K0>(x0, x1, v, W, dst, store);
+        WvUnroll<CR, K0 + 1, N - 1>::run(x0, x1, v, W, dst, store);
+    }
+};
+template <int CR, int K0>
+struct WvUnroll<CR, K0, 0> {
+    static __device__ __forceinline__ void run(float&, float&, const float*, const WvLane&, uint2*, bool) {}
+};
+
+template <int CR>
+__device__ __forceinline__ void wv_load(const float* __restrict__ llr, int b, float* v)
+{
+    enum { NF = WvBody<CR>::NF, VW = WvBody<CR>::VW };
+    if (VW == 4) {
+        const float4* src = reinterpret_cast<const float4*>(llr) + (size_t)b * (NF / 4);
+#pragma unroll
+        for (int k = 0; k < NF / 4; k++) {
+            const float4 x = __ldg(src + k);
+            v[4 * k] = x.x;
+            v[4 * k + 1] = x.y;
+            v[4 * k + 2] = x.z;
+            v[4 * k + 3] = x.w;
+        }
+    } else {
+        const float2* src = reinterpret_cast<const float2*>(llr) + (size_t)b * (NF / 2);
+#pragma unroll
+        for (int k = 0; k < NF / 2; k++) {
+            const float2 x = __ldg(src + k);
+            v[2 * k] = x.x;
+            v[2 * k + 1] = x.y;
+        }
+    }
+}
+
+/* one tail step with run-time phase */
+__device__ __forceinline__ uint2 wv_step_rt(int ph, float& x0, float& x1, float t0, float t1, const WvLane& W)
+{
+    switch (ph) {
+    case 0: return wv_step<0, MASK_FULL>(x0, x1, t0, t1, W);
+    case 1: return wv_step<1, MASK_FULL>(x0, x1, t0, t1, W);
+    case 2: return wv_step<2, MASK_FULL>(x0, x1, t0, t1, W);
+    case 3: return wv_step<3, MASK_FULL>(x0, x1, t0, t1, W);
+    default: return wv_step<4, MASK_FULL>(x0, x1, t0, t1, W);
+    }
+}
+
+#ifndef WV_MINBLK
+#define WV_MINBLK 16
+#endif
+template <int CR>
+__global__ void __launch_bounds__(32, WV_MINBLK) viterbi_warp_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
+                                                                      const w80211_desc* __restrict__ desc, const float* __restrict__ llr,
+                                                                      uint2* __restrict__ surv, int slot0)
+{
+    enum { STEPS = WvBody<CR>::STEPS, NF = WvBody<CR>::NF };
+    const int slot = slot0 + blockIdx.x, lane = threadIdx.x;
+    const int pkt = slot_pkt[slot];
+    if (pkt < 0) return;
+    const int4 G = grp[slot >> 5];
+    const int trellis = desc[pkt].trellis;
+    const float* __restrict__ l = llr + desc[pkt].llr_off;
+    uint2* __restrict__ s = surv + (size_t)G.x * 32 + (size_t)(slot & 31) * G.y;
+    WvLane W;
+    wv_setup(lane, W);
+    const float NEG = -1000000000000000.0f; /* vstb_init, decode_impl.cc:174-177 */
+    float x0 = lane == 0 ? 0.0f : NEG, x1 = NEG;
+    const bool store = lane == 0;
+    const int nbody = trellis / STEPS;
+    float cur[NF], nxt[NF];
+    if (nbody > 0) {
+        wv_load<CR>(l, 0, cur);
+    } else {
+#pragma unroll
+        for (int k = 0; k < NF; k++) cur[k] = 0.f;
+    }
+    for (int b = 0; b < nbody; b++) {
+        const int bn = b + 1 < nbody ? b + 1 : b;
+        wv_load<CR>(l, bn, nxt);
+        if (b + VIT_PF < nbody) asm volatile("prefetch.global.L2 [%0];" ::"l"(l + (size_t)(b + VIT_PF) * NF));
+        WvUnroll<CR, 0, STEPS>::run(x0, x1, cur, W, s + (size_t)b * STEPS, store);
+#pragma unroll
+        for (int k = 0; k < NF; k++) cur[k] = nxt[k];
+    }
+    /* tail: fewer than STEPS steps; an absent LLR is an explicit 0.0f as in the reference */
+    const int period = wv_period<CR>();
+    const float* q = l + (size_t)nbody * NF;
+    int ph = 0;
+    for (int t = nbody * STEPS; t < trellis; t++) {
+        const bool hasA = ph == 0 || (ph & 1), hasB = ph == 0 || !(ph & 1);
+        float t0 = 0.0f, t1 = 0.0f;
+        if (hasA) t0 = __ldg(q++);
+        if (hasB) t1 = __ldg(q++);
+        const uint2 w = wv_step_rt(t % 5, x0, x1, t0, t1, W);
+        if (store) s[t] = w;
+        if (++ph >= period) ph = 0;
+    }
+}
+
+/* vstb_end (decode_impl.cc:282-302) for the layout above, one warp per packet, exact and parallel.
+ *
+ * The trellis is cut into 32 chunks of W steps (W a multiple of 32), lane c walks chunk c backwards.  Only the last
+ * chunk knows its entry position (state 0 at the end of the trellis = lane 0, register 0); every other lane starts with
+ * the SET of all 64 positions and propagates the set through the survivor words (a handful of bitwise operations per
+ * step, see below).  Survivor paths merge: after a few dozen steps the set has one member, and from there on the walk
+ * is the true path whatever the entry was.  So: (1) all lanes walk `m` steps in set mode, m a multiple of 32, until
+ * every lane's set is a single position; (2) they walk the rest of their chunk as a chain and emit its decoded bits;
+ * (3) each lane now knows the position at the bottom of its chunk, which is the entry of the chunk below: one shuffle
+ * hands it down and the top m steps of every chunk are walked again as a chain from the true entry.  If some set
+ * never shrinks to one member inside its chunk (decisions that map positions one-to-one for a thousand steps;
+ * not seen with real LLRs), lane 0 walks the whole trellis alone: the result is exact either way.
+ *
+ * Set step, phase j: members whose decision bit is 0 came from the even source, 1 from the odd one; the predecessor of
+ * (lane, r) is (lane with bit j := dec, r' = old bit j of lane).  With Z / O the members with dec 0 / 1 (both registers
+ * folded) and Mj the lanes with bit j set:  S0' = (Z & ~Mj) | ((O & ~Mj) << 2^j),  S1' = ((Z & Mj) >> 2^j) | (O & Mj). */
+struct TbPos {
+    uint32_t l, r;
+};
+__device__ __forceinline__ void tb_chain_step(TbPos& p, uint2 w, int j, uint32_t& word, int bitpos)
+{
+    word |= p.r << bitpos;
+    const uint32_t sel = p.r ? w.y : w.x;
+    const uint32_t dec = (sel >> p.l) & 1u;
+    const uint32_t m = 1u << j;
+    p.r = (p.l >> j) & 1u;
+    p.l = (p.l & ~m) | (dec << j);
+}
+__device__ __forceinline__ void tb_set_step(uint32_t& s0, uint32_t& s1, uint2 w, int j)
+{
+    const uint32_t Mj = j == 0 ? 0xAAAAAAAAu : (j == 1 ? 0xCCCCCCCCu : (j == 2 ? 0xF0F0F0F0u : (j == 3 ? 0xFF00FF00u : 0xFFFF0000u)));
+    const uint32_t Z = (s0 & ~w.x) | (s1 & ~w.y), O = (s0 & w.x) | (s1 & w.y);
+    const int sh = 1 << j;
+    s0 = (Z & ~Mj) | ((O & ~Mj) << sh);
+    s1 = ((Z & Mj) >> sh) | (O & Mj);
+}
+
+/* 16 steps t0+15 .. t0 (t0 a multiple of 16) of one lane's chunk; steps >= T do not exist */
+template <bool SET>
+__device__ __forceinline__ void tb_block16(const uint2* __restrict__ s, int t0, int T, TbPos& p, uint32_t& s0, uint32_t& s1, uint32_t& word)
+{
+    uint4 w[8];
+    const uint4* s4 = reinterpret_cast<const uint4*>(s + t0);
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+        if (t0 + 2 * k < T) w[k] = __ldg(s4 + k);
+    const int sh = t0 & 16;
+    int ph = (t0 + 15) % 5;
+#pragma unroll
+    for (int k = 15; k >= 0; k--) {
+        const int j = ph == 0 ? 4 : ph - 1;
+        if (t0 + k < T) {
+            const uint2 sw = (k & 1) ? make_uint2(w[k >> 1].z, w[k >> 1].w) : make_uint2(w[k >> 1].x, w[k >> 1].y);
+            if (SET)
+                tb_set_step(s0, s1, sw, j);
+            else
+                tb_chain_step(p, sw, j, word, sh + k);
+        }
+        ph = ph == 0 ? 4 : ph - 1;
+    }
+}
+
+__global__ void __launch_bounds__(32, 16) traceback_warp_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
+                                                                 const w80211_desc* __restrict__ desc, const uint2* __restrict__ surv,
+                                                                 uint32_t* __restrict__ bits, int slot0)
+{
+    const int slot = slot0 + blockIdx.x, lane = threadIdx.x;
+    const int pkt = slot_pkt[slot];
+    if (pkt < 0) return;
+    const int4 G = grp[slot >> 5];
+    const int T = desc[pkt].trellis;
+    const uint2* __restrict__ s = surv + (size_t)G.x * 32 + (size_t)(slot & 31) * G.y;
+    uint32_t* __restrict__ out = bits + (size_t)G.z * 32 + (slot & 31);
+    /* steps per chunk, a multiple of 32 with 32 * W >= T; at least 256 so that short packets use fewer, longer chunks
+     * (survivor paths need a few dozen steps to merge, more at low SNR) */
+    const int W = max(((T + 1023) >> 10) << 5, 256);
+    const int lo = lane * W, hi = lo + W;  /* this lane's steps [lo, hi) */
+    /* (1) set mode from the top of the chunk */
+    uint32_t s0 = hi >= T ? 1u : 0xffffffffu, s1 = hi >= T ? 0u : 0xffffffffu;
+    TbPos p = {0u, 0u};
+    uint32_t word = 0;
+    int m = 0;
+    bool merged = false;
+    while (m < W) {
+        tb_block16<true>(s, hi - m - 16, T, p, s0, s1, word);
+        tb_block16<true>(s, hi - m - 32, T, p, s0, s1, word);
+        m += 32;
+        merged = __popc(s0) + __popc(s1) == 1;
+        if (__all_sync(WV_FULL, merged)) break;
+    }
+    const bool all_merged = __all_sync(WV_FULL, merged);
+    if (all_merged) {
+        /* (2) the rest of the chunk as a chain */
+        p.r = s1 ? 1u : 0u;
+        p.l = (uint32_t)__ffs((int)(s0 | s1)) - 1u;
+        for (int t = hi - m - 32; t >= lo; t -= 32) {
+            word = 0;
+            tb_block16<false>(s, t + 16, T, p, s0, s1, word);
+            tb_block16<false>(s, t, T, p, s0, s1, word);
+            if (t < T) out[(size_t)(t >> 5) * 32] = word;
+        }
+        /* (3) the top m steps again, from the position the chunk above ended at */
+        uint32_t el = __shfl_down_sync(WV_FULL, p.l, 1), er = __shfl_down_sync(WV_FULL, p.r, 1);
+        if (lane == 31) el = er = 0u;
+        p.l = el;
+        p.r = er;
+        for (int t = hi - 32; t >= hi - m; t -= 32) {
+            word = 0;
+            tb_block16<false>(s, t + 16, T, p, s0, s1, word);
+            tb_block16<false>(s, t, T, p, s0, s1, word);
+            if (t < T) out[(size_t)(t >> 5) * 32] = word;
+        }
+    } else if (lane == 0) {
+        p.l = p.r = 0u;
+        for (int t = ((T - 1) >> 5) << 5; t >= 0; t -= 32) {
+            word = 0;
+            tb_block16<false>(s, t + 16, T, p, s0, s1, word);
+            tb_block16<false>(s, t, T, p, s0, s1, word);
+            out[(size_t)(t >> 5) * 32] = word;
+        }
+    }
+}
+
+/* warp_mask: bit cr set = that code rate's groups use the warp-per-packet kernels (forward pass and traceback must agree:
+ * the survivor layouts differ) */
 int w_launch_viterbi(cudaStream_t st, const int* cr_first /* [5]: first group of each code rate, [4] = ngroups */, const int4* grp,
-                     const int* slot_pkt, const w80211_desc* desc, const float* llr, uint2* surv)
+                     const int* slot_pkt, const w80211_desc* desc, const float* llr, uint2* surv, int warp_mask)
 {
     int launches = 0;
     for (int cr = 0; cr < 4; cr++) {
         int n = cr_first[cr + 1] - cr_first[cr];
         if (n <= 0) continue;
         launches++;
+        const int g0 = cr_first[cr];
+        if ((warp_mask >> cr) & 1) {
+            switch (cr) {
+            case W80211_CR_12: viterbi_warp_kernel<W80211_CR_12><<<n * 32, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0 * 32); break;
+            case W80211_CR_23: viterbi_warp_kernel<W80211_CR_23><<<n * 32, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0 * 32); break;
+            case W80211_CR_34: viterbi_warp_kernel<W80211_CR_34><<<n * 32, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0 * 32); break;
+            default: viterbi_warp_kernel<W80211_CR_56><<<n * 32, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0 * 32); break;
+            }
+            continue;
+        }
         switch (cr) {
-        case W80211_CR_12: viterbi_kernel<W80211_CR_12><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
-        case W80211_CR_23: viterbi_kernel<W80211_CR_23><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
-        case W80211_CR_34: viterbi_kernel<W80211_CR_34><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
-        default: viterbi_kernel<W80211_CR_56><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, cr_first[cr]); break;
+        case W80211_CR_12: viterbi_kernel<W80211_CR_12><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0); break;
+        case W80211_CR_23: viterbi_kernel<W80211_CR_23><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0); break;
+        case W80211_CR_34: viterbi_kernel<W80211_CR_34><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0); break;
+        default: viterbi_kernel<W80211_CR_56><<<n, 32, 0, st>>>(grp, slot_pkt, desc, llr, surv, g0); break;
         }
     }
     return launches;
 }
 
-void w_launch_traceback(cudaStream_t st, int ngroups, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
-                        const uint2* surv, uint32_t* bits)
+/* one launch per run of code rates that share a survivor layout */
+int w_launch_traceback(cudaStream_t st, const int* cr_first, const int4* grp, const int* slot_pkt, const w80211_desc* desc,
+                       const uint2* surv, uint32_t* bits, int warp_mask)
 {
-    if (ngroups <= 0) return;
-    traceback_kernel<<<ngroups, 32, 0, st>>>(grp, slot_pkt, desc, surv, bits);
+    int launches = 0;
+    for (int cr = 0; cr < 4;) {
+        const int w = (warp_mask >> cr) & 1;
+        int c2 = cr + 1;
+        while (c2 < 4 && ((warp_mask >> c2) & 1) == w) c2++;
+        const int g0 = cr_first[cr], n = cr_first[c2] - g0;
+        cr = c2;
+        if (n <= 0) continue;
+        launches++;
+        if (w)
+            traceback_warp_kernel<<<n * 32, 32, 0, st>>>(grp, slot_pkt, desc, surv, bits, g0 * 32);
+        else
+            traceback_kernel<<<n, 32, 0, st>>>(grp, slot_pkt, desc, surv, bits, g0);
+    }
+    return launches;
 }

@@ -173,6 +173,27 @@ def vht_ampdu(mpdus):
     return out
 
 
+def vht_ampdu_multi(mpdus, zero_delims=0):
+    """A-MPDU of several subframes for ONE packet: `mpdus` is a list of uint8 arrays (an empty array is a zero-length
+    delimiter), EOF is set on the last subframe only; `zero_delims` zero-length delimiters (EOF 0) follow every subframe
+    but the last.  Returns [1, nbytes].  The reference's walk ORs each delimiter's length into a value that survives
+    from the subframe before (+4 after an FCS pass, decode_impl.cc:345-351,414), so consecutive subframes decode cleanly
+    only when each length has all the bits of (previous length + 4) set, e.g. lengths growing by 4."""
+    parts = []
+    for i, m in enumerate(mpdus):
+        a = vht_ampdu(np.asarray(m, np.uint8)[None, :])[0].copy()
+        last = i == len(mpdus) - 1
+        if not last:
+            a[0] &= 0xFE
+        parts.append(a)
+        if not last:
+            for _ in range(zero_delims):
+                z = vht_ampdu(np.zeros((1, 0), np.uint8))[0].copy()
+                z[0] &= 0xFE
+                parts.append(z)
+    return np.concatenate(parts)[None, :]
+
+
 # --------------------------------------------------------------- OFDM level
 def _seq(s):
     return np.array([int(c) for c in s.replace("-", "n").replace("n1", "-1 ").replace("1", "1 ").replace("0", "0 ").split()])

@@ -86,7 +86,7 @@ def vht_siga_bits_mu(gid, short_gi):
 
 def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, chan=None, nrx=None,
               mpdus=None, corrupt_sig=False, corrupt_fcs=False, l_len_short=0, lead=0, trail=0,
-              ndp=False, mu_pos=None, mu_gid=2):
+              ndp=False, mu_pos=None, mu_gid=2, psdu=None):
     """Generate npkt packets of one configuration.
 
     length: PSDU bytes for legacy / HT; MPDU bytes for VHT (wrapped in a one-subframe A-MPDU, so the
@@ -96,6 +96,8 @@ def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, 
     corrupt_sig: flip one HT-SIG / VHT-SIG-A bit after the CRC was computed (dropped by the SIG check).
     corrupt_fcs: flip one payload bit (packet decodes, FCS fails).
     l_len_short: subtract this many OFDM symbols from the L-SIG duration (dropped by the length gate).
+    psdu:   VHT only: a ready-made PSDU [npkt, nbytes] (a multiple of 4 bytes, e.g. from gen.vht_ampdu_multi) sent as it is
+            instead of the one-subframe A-MPDU built from `mpdus`.
     ndp:    VHT null data packet (sounding): no data field, the NDP pattern in VHT-SIG-B.
     mu_pos: 0 or 1: a VHT MU PPDU (group id mu_gid) as the user at that position receives it once the other user's
             stream is nulled: legacy part and VHT-SIG-A from chain 0, then VHT-STF, two VHT-LTFs with row mu_pos of the
@@ -103,11 +105,15 @@ def gen_batch(fmt, mcs, nss, length, npkt, snr_db=None, short_gi=False, seed=0, 
     Returns a dict, see the bottom of this function."""
     rng = np.random.default_rng(seed)
     if mpdus is None:
-        mpdus = g.make_mpdus(npkt, length, rng)
+        mpdus = g.make_mpdus(npkt, length, rng) if psdu is None else np.zeros((npkt, 0), np.uint8)
     if corrupt_fcs:
         mpdus = mpdus.copy()
         mpdus[:, length // 2] ^= 0x10
-    psdu = g.vht_ampdu(mpdus) if fmt == g.F_VHT else mpdus
+    if psdu is not None:
+        assert fmt == g.F_VHT and psdu.shape[0] == npkt and psdu.shape[1] % 4 == 0
+        psdu = np.ascontiguousarray(psdu, np.uint8)
+    else:
+        psdu = g.vht_ampdu(mpdus) if fmt == g.F_VHT else mpdus
     m = g.Mod(fmt, mcs, nss, psdu.shape[1], short_gi)
     nrx = nrx or m.nss
     streams, bits = g.data_field_bits(m, psdu)

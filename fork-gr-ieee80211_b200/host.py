@@ -219,10 +219,11 @@ class Result:
 class Receiver:
     """One w80211_ctx (one GPU)."""
 
-    def __init__(self, device=0, nslots=2):
+    def __init__(self, device=0, nslots=2, viterbi="auto"):
+        """viterbi: "auto" | "thread" | "warp" -- which Viterbi kernels decode (w80211_cfg.flags, W80211_CFG_VITERBI_*)."""
         self.L = load()
         self.h = C.c_void_p()
-        cfg = Cfg(device, 0, nslots, 0)
+        cfg = Cfg(device, 0, nslots, {"auto": 0, "thread": 1, "warp": 2}[viterbi])
         r = self.L.w80211_create(C.byref(cfg), C.byref(self.h))
         if r != 0:
             raise W80211Error("w80211_create failed (%d): no usable CUDA device; this library has no CPU path" % r)

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define W80211_ABI_VERSION 5
+#define W80211_ABI_VERSION 6
 
 /* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
 #define W80211_F_L 0
@@ -81,8 +81,17 @@ typedef struct w80211_cfg {
     int32_t device;        /* CUDA device ordinal */
     int32_t max_packets;   /* capacity hint per batch (grown on demand) */
     int32_t nslots;        /* double buffering depth for rx_submit/collect: 1..4 (0 = 2) */
-    int32_t flags;         /* reserved, 0 */
+    int32_t flags;         /* W80211_CFG_* below, 0 = defaults */
 } w80211_cfg;
+
+/* w80211_cfg.flags, bits 0-1: which Viterbi kernels decode a code-rate group (both are bit-exact, tests run every parity
+ * case under both).  AUTO: one warp per packet (64 path metrics over the 32 lanes, ballot survivors, parallel exact
+ * traceback) while a launch has too few packets to give every lane of the GPU a packet of its own, else one thread per
+ * packet; the crossover is W80211_WARP_MAX_PKTS packets per code rate (environment, default 7168). */
+#define W80211_CFG_VITERBI_AUTO 0
+#define W80211_CFG_VITERBI_THREAD 1 /* always one thread per packet (csrc/viterbi.cu viterbi_kernel) */
+#define W80211_CFG_VITERBI_WARP 2   /* always one warp per packet (viterbi_warp_kernel) */
+#define W80211_CFG_VITERBI_MASK 3
 
 /* One packet as the reference's signal / signal2 block hands it over
  * (tags written at lib/signal_impl.cc:135-152). */
@@ -145,8 +154,10 @@ typedef struct w80211_batch_out {
     uint8_t* bytes;          /* decoded, descrambled PSDU bytes of all packets, packet p at psdu_off[p] */
     uint64_t bytes_capacity;
     uint32_t* psdu_off;      /* [npkt] byte offset of bit 16 (first PSDU byte) of packet p in bytes */
-    w80211_mpdu* mpdus;      /* [mpdu_capacity], sorted by (pkt, off) */
-    uint32_t mpdu_capacity;
+    w80211_mpdu* mpdus;      /* [mpdu_capacity], sorted by (pkt, off); NULL: records are counted but not returned */
+    uint32_t mpdu_capacity;  /* one record per legacy / HT packet; a VHT packet yields one per A-MPDU delimiter the reference's walk
+                                visits, FCS-valid or not (zero-length ones included): at most trellis / 32 + 1.  A batch with more
+                                records than this returns W80211_E_CAPACITY; the library's own buffers grow to the exact count */
     float* llr;              /* [llr_capacity] or NULL */
     uint64_t llr_capacity;
     /* results (host side) */

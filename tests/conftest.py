@@ -21,10 +21,12 @@ def refgr():
     return r
 
 
-@pytest.fixture(scope="session")
-def rx():
-    """One w80211_ctx on cuda:0, through the C ABI.  Fails (does not skip) when the library is missing."""
+@pytest.fixture(scope="session", params=["thread", "warp"])
+def rx(request):
+    """One w80211_ctx on cuda:0, through the C ABI.  Fails (does not skip) when the library is missing.
+    Every test that decodes runs twice: with the one-thread-per-packet Viterbi kernels and with the one-warp-per-packet
+    ones (w80211_cfg.flags); both must equal the reference bit for bit."""
     import w80211rx
-    r = w80211rx.host.Receiver(0)
+    r = w80211rx.host.Receiver(0, viterbi=request.param)
     yield r
     r.close()

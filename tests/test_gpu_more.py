@@ -1,6 +1,7 @@
 """More GPU parity: the reference's golden fixtures, 2x2, drop gates, ragged / empty batches,
 A-MPDUs with several subframes, the split demod / decode entry points, and size-independent
 properties at full batch size."""
+import ctypes as C
 import os
 import zlib
 
@@ -113,24 +114,61 @@ def test_bad_descriptor_is_flagged_not_crashing(rx):
 
 
 def test_vht_ampdu_several_subframes(refgr, rx):
-    """A-MPDU with three subframes (and a zero-length delimiter in between): the delimiter walk of
-    decode_impl.cc:336-426 including its length-accumulation quirk."""
+    """A-MPDU with three subframes: the delimiter walk of decode_impl.cc:336-426 including its length-accumulation
+    quirk (each length has all the bits of the previous length + 4, so all three pass)."""
     rng = np.random.default_rng(9)
     mp = [g.make_mpdus(1, n, rng)[0] for n in (64, 68, 200)]
-    parts = []
-    for i, m in enumerate(mp):
-        a = g.vht_ampdu(m[None, :])[0].copy()
-        if i < len(mp) - 1:
-            a[0] &= 0xFE  # EOF only on the last subframe
-        parts.append(a)
-    psdu = np.concatenate(parts)
-    length = len(psdu) - 4  # gen_batch wraps `mpdus` in one more delimiter; feed the body as the MPDU instead
-    body = psdu[4:][None, :]
-    # first delimiter is rebuilt by vht_ampdu for a length-`length` MPDU: replace it after generation is not possible,
-    # so build the batch from a hand-made PSDU through the lower-level entry
-    b = gp.gen_batch(g.F_VHT, 4, 1, length, 1, snr_db=30, seed=50, mpdus=body)
+    b = gp.gen_batch(g.F_VHT, 4, 1, 0, 1, snr_db=30, seed=50, psdu=g.vht_ampdu_multi(mp))
     res, msgs = compare_with_reference(refgr, rx, [b])
-    assert res.n_mpdu >= 1
+    assert res.n_mpdu == 3 and res.n_crc_ok == 3
+    assert [m[3:-1] for m in msgs] == [x.tobytes() for x in mp]
+
+
+def test_vht_ampdu_zero_length_delimiters_between_subframes(refgr, rx):
+    """Zero-length delimiters after a subframe: the reference ORs them into the length it carries over, walks the rest
+    with that length and publishes only the first subframe; every delimiter it visits is a record here."""
+    rng = np.random.default_rng(10)
+    mp = [g.make_mpdus(1, n, rng)[0] for n in (64, 68, 72)]
+    b = gp.gen_batch(g.F_VHT, 4, 1, 0, 1, snr_db=30, seed=51, psdu=g.vht_ampdu_multi(mp, zero_delims=2))
+    res, msgs = compare_with_reference(refgr, rx, [b])
+    assert len(msgs) == 1 and res.n_crc_ok == 1 and res.n_mpdu > 1
+
+
+def test_vht_ampdu_many_subframes_outgrow_the_record_buffers(refgr, rx):
+    """36 subframes per PPDU in 8 PPDUs: 288 MPDU records against library buffers that start at 1.5 per packet
+    (the post kernel runs once more with the exact count); all 288 are published like the reference does.  Then the same
+    batch with out->mpdus = NULL: counted, not returned, no capacity error."""
+    rng = np.random.default_rng(11)
+    ps = np.concatenate([g.vht_ampdu_multi([g.make_mpdus(1, n, rng)[0] for n in range(28, 28 + 4 * 36, 4)]) for _ in range(8)])
+    b = gp.gen_batch(g.F_VHT, 4, 1, 0, 8, snr_db=30, seed=52, psdu=ps)
+    res, msgs = compare_with_reference(refgr, rx, [b])
+    assert res.n_mpdu == 288 and res.n_crc_ok == 288 and len(msgs) == 288
+    iq, pkts, chan = host.pack_batch([b])
+    bi = rx.make_in(iq, pkts, chan)
+    bo, arrs = rx.make_out_host(len(pkts), 8 * 4096, 1)
+    bo.mpdus, bo.mpdu_capacity = None, 0
+    rx._check(rx.L.w80211_rx_batch(rx.h, C.byref(bi), C.byref(bo)))
+    assert bo.n_mpdu == 288 and bo.n_crc_ok == 288 and bo.psdu_bits_ok == res.psdu_bits_ok
+    # a caller buffer that is too small is an error the caller can see, and the context stays usable
+    bo2, arrs2 = rx.make_out_host(len(pkts), 8 * 4096, 100)
+    assert rx.L.w80211_rx_batch(rx.h, C.byref(bi), C.byref(bo2)) == -5
+    res3 = rx.rx(iq, pkts, chan)
+    assert res3.n_crc_ok == 288
+
+
+def test_psdu_of_zero_length_delimiters_only(refgr, rx):
+    """A 4 KB PSDU of nothing but zero-length delimiters: about a thousand records per packet, none valid; the reference
+    publishes nothing and neither do we (the ADVICE case: records far beyond two per packet)."""
+    z = g.vht_ampdu(np.zeros((1, 0), np.uint8))[0].copy()
+    z[0] &= 0xFE
+    ps = np.tile(z, 1000)[None, :]
+    b = gp.gen_batch(g.F_VHT, 8, 1, 0, 1, snr_db=30, seed=53, psdu=ps)
+    iq, pkts, chan = host.pack_batch([b])
+    bi = rx.make_in(iq, pkts, chan)
+    bo, arrs = rx.make_out_host(1, 4096 + 64, 1100)
+    rx._check(rx.L.w80211_rx_batch(rx.h, C.byref(bi), C.byref(bo)))
+    ref_pkts, ref_msgs = ref_chain(refgr, [b])
+    assert ref_msgs == [] and bo.n_crc_ok == 0 and bo.n_mpdu >= 1000  # the symbol padding after the PSDU reads as more of them
 
 
 def test_split_entry_points_equal_fused(refgr, rx):
