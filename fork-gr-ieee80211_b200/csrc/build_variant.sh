@@ -1,7 +1,7 @@
 #!/bin/sh
 # Tuning helper: build a kernel variant of the library next to the product one.
 #   ./build_variant.sh NAME -DVIT_MINBLK=12 -DDEMOD_MINBLK=6 ...   ->  ../variants/libw80211rx_NAME.so
-# Select it with W80211_LIB=<path>; never used by tests or the default bench.
+# Select it with bench.py --resident-only --lib <path>; never used by tests or the default bench.
 set -e
 cd "$(dirname "$0")"
 name=$1; shift

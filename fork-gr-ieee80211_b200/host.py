@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("W80211_LIB") or os.path.join(_HERE, "libw80211rx.so")  # W80211_LIB: kernel-variant builds (tuning only)
+LIB_PATH = os.path.join(_HERE, "libw80211rx.so")  # the product library; bench.py --resident-only --lib points tuning runs at a variant build
 
 MEM_HOST, MEM_DEVICE = 0, 1
 ST_OK, ST_DROP_GATE, ST_NDP, ST_UNSUPPORTED, ST_BAD_INPUT = 0, 1, 2, 3, 4
