@@ -49,6 +49,11 @@ CONFIGS = {
            "nss": 1, "length": 4088, "short_gi": False, "payload": 4088, "idx": 4},
     "C5": {"workload": "C5: HT MCS15 64-QAM r5/6 2SS 2x2 long-GI (demod2, zero forcing), 4095 B, AWGN 30 dB, 20 MHz", "fmt": "HT", "mcs": 15,
            "nss": 2, "length": 4095, "short_gi": False, "payload": 4095, "idx": 5},
+    # tuning only (--resident-only): the two code rates no BASELINE configuration exercises
+    "T12": {"workload": "T12 (tuning): VHT MCS3 16-QAM r1/2 1SS, MPDU 2040 B", "fmt": "VHT", "mcs": 3, "nss": 1, "length": 2040,
+            "short_gi": False, "payload": 2040, "idx": 6},
+    "T23": {"workload": "T23 (tuning): VHT MCS5 64-QAM r2/3 1SS, MPDU 4000 B", "fmt": "VHT", "mcs": 5, "nss": 1, "length": 4000,
+            "short_gi": False, "payload": 4000, "idx": 7},
 }
 CONFIG = "C4"   # the configuration of `value`; --config changes it for --resident-only tuning runs
 MPDU_LEN = 4088  # --mpdu-len: profiling variants of C4 only
@@ -766,7 +771,7 @@ def main():
     ap.add_argument("--cpu-packets", type=int, default=128, help="packets per core of the cpu_baseline sample inside the GPU arm")
     ap.add_argument("--blocks-packets", type=int, default=4096, help="packets of the e2e_blocks leg")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--config", default="C4", choices=["C2", "C3", "C4", "C5"],
+    ap.add_argument("--config", default="C4", choices=["C2", "C3", "C4", "C5", "T12", "T23"],
                     help="tuning runs (with --resident-only): another configuration of BASELINE.json as the main workload; the benchmark's is C4 "
                          "and the others are reported under `configs`")
     ap.add_argument("--resident-only", action="store_true", help="tuning runs: the resident leg and the per-kernel times only, short JSON line")

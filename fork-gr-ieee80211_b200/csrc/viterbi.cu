@@ -1,32 +1,45 @@
-/* viterbi.cu -- soft-decision K=7 Viterbi decoder, one THREAD per packet.
+/* viterbi.cu -- soft-decision K=7 Viterbi decoder: forward pass and traceback, in two layouts.
  *
  * Replaces decode_impl::vstb_init / vstb_update / vstb_end (lib/decode_impl.cc:164-302).
  *
- * Why one thread per packet.  The reference's result is defined by one sequential FP32
- * add-compare-select chain per packet (no renormalisation, strict '>' with the even source
- * first, full-length traceback from state 0).  Splitting a packet into overlapped windows
- * changes the FP32 sums and is not provably bit-exact, and a warp-per-packet butterfly spends
- * more issue slots on shuffles, selects and ballots than on the ACS itself.  With the whole
- * trellis of a packet in one thread all 64 path metrics live in registers, every branch label
- * is a compile-time constant (adds of an absent or zero branch metric disappear), there is no
- * cross-lane traffic at all, and the parallelism comes from the batch: 32 packets per warp,
- * thousands of packets per launch.  Arithmetic per step and state: <= 2 FADD (candidates),
- * 1 FADD (difference, whose sign is the decision), 1 FMNMX, 1 SHF (decision bit into a word).
+ * The reference's result is defined by one sequential FP32 add-compare-select chain per packet (no renormalisation,
+ * strict '>' with the even source first, full-length traceback from state 0).  Both layouts keep exactly that chain per
+ * state (two rounded candidate sums, their comparison, their maximum), so decisions and metrics are the reference's bit
+ * for bit; overlapped windows would change which sums are formed and are not used.
  *
- * Survivors: one 64-bit word per step and packet, bit d = 1 when destination state d took its
- * odd source 2(d&31)+1.  Layout [group of 32 packets][step pair][lane] as uint4 so that a warp
- * stores and the traceback kernel loads 512 contiguous bytes.
+ *  - one THREAD per packet (viterbi_kernel, traceback_kernel): all 64 path metrics of a packet live in one thread's
+ *    registers, every branch label is a compile-time constant (adds of an absent or zero branch metric disappear), no
+ *    cross-lane traffic; the parallelism comes from the batch (32 packets per warp, 56 832 per wave).  Per state and step:
+ *    <= 2 FADD (candidates), 1 FADD (difference, whose sign is the decision), 1 FMNMX, 1 SHF (decision bit into a word).
+ *    Survivors: one 64-bit word per step and packet, bit d = 1 when destination state d took its odd source 2(d&31)+1,
+ *    laid out [group of 32 packets][step pair][lane] as uint4 so a warp stores / loads 512 contiguous bytes.
+ *  - one WARP per packet (viterbi_warp_kernel, traceback_warp_kernel, second half of this file): two metrics per lane,
+ *    one shuffle exchange per step, survivors by ballot, exact parallel traceback.  For launches that cannot give every
+ *    lane of the GPU a packet of its own (a single C4 packet: 1.3 ms instead of 7.4).
+ * The host plan picks per code-rate group (capi.cu, w80211_cfg.flags).
  *
- * Depuncturing (decode_impl.cc:210-229) is folded into the step template: a punctured
- * position contributes exactly 0.0f in the reference, i.e. the add is skipped here.
+ * Depuncturing (decode_impl.cc:210-229) is folded into the step templates: a punctured position contributes exactly
+ * 0.0f in the reference, i.e. the add is skipped here.
  */
 #include "common.cuh"
 
 #ifndef VIT_MINBLK
 #define VIT_MINBLK 12 /* one-warp blocks per SM: 12 -> 168 registers, no spills; measured best (profiles/r1_viterbi_sweep.txt) */
 #endif
-#ifndef VIT_INPLACE
-#define VIT_INPLACE 1
+/* trellis steps per unrolled loop body of the thread-per-packet kernel, per code rate: a whole number of puncturing
+ * periods (1, 2, 3, 5 steps).  Measured on B200 (profiles/experiments/r2_viterbi_body_length.txt): six steps for rates 1/2, 2/3
+ * and 3/4 (the state <-> register map closes by itself), five for rate 5/6 (closed by a register permutation) */
+#ifndef VIT_STEPS_12
+#define VIT_STEPS_12 6
+#endif
+#ifndef VIT_STEPS_23
+#define VIT_STEPS_23 6
+#endif
+#ifndef VIT_STEPS_34
+#define VIT_STEPS_34 6
+#endif
+#ifndef VIT_STEPS_56
+#define VIT_STEPS_56 5
 #endif
 #ifndef VIT_PF
 #define VIT_PF 8 /* L1 prefetch distance, in bodies */
@@ -42,70 +55,6 @@ __device__ __forceinline__ float add_label(float m, int l, float t0, float t1, f
     if (MASK == MASK_FULL) return l == 0 ? m : __fadd_rn(m, l == 1 ? t1 : (l == 2 ? t0 : t3));
     if (MASK == MASK_A) return (l & 2) ? __fadd_rn(m, t0) : m;
     return (l & 1) ? __fadd_rn(m, t1) : m;
-}
-
-template <int MASK>
-__device__ __forceinline__ void acs(const float (&m)[64], float (&n)[64], float t0, float t1, uint32_t& lo, uint32_t& hi)
-{
-    const float t3 = MASK == MASK_FULL ? __fadd_rn(t1, t0) : 0.0f;
-    lo = 0;
-    hi = 0;
-#pragma unroll
-    for (int s = 31; s >= 0; s--) {
-        const int L = w_branch_label(2 * s, 0); /* label of 2s --0--> s; the other three follow by complement */
-        const float ma = m[2 * s], mb = m[2 * s + 1];
-        /* destination s (input bit 0): even source first, as the reference visits sources in ascending order */
-        float c0 = add_label<MASK>(ma, L, t0, t1, t3);
-        float c1 = add_label<MASK>(mb, 3 - L, t0, t1, t3);
-        n[s] = fmaxf(c0, c1);
-        lo = __funnelshift_l(__float_as_uint(__fsub_rn(c0, c1)), lo, 1); /* sign(c0-c1) = (c1 > c0) */
-        /* destination s+32 (input bit 1) */
-        float e0 = add_label<MASK>(ma, 3 - L, t0, t1, t3);
-        float e1 = add_label<MASK>(mb, L, t0, t1, t3);
-        n[s + 32] = fmaxf(e0, e1);
-        hi = __funnelshift_l(__float_as_uint(__fsub_rn(e0, e1)), hi, 1);
-    }
-}
-
-/* two steps m -> n -> m and one 16-byte survivor store */
-template <int M0, int M1>
-__device__ __forceinline__ void acs2(float (&m)[64], float (&n)[64], float a0, float a1, float b0, float b1, uint4* dst)
-{
-    uint4 w;
-    acs<M0>(m, n, a0, a1, w.x, w.y);
-    acs<M1>(n, m, b0, b1, w.z, w.w);
-    *dst = w;
-}
-
-template <int CR> struct Body;
-template <> struct Body<W80211_CR_12> { enum { STEPS = 4, NV = 2 }; };
-template <> struct Body<W80211_CR_23> { enum { STEPS = 8, NV = 3 }; };
-template <> struct Body<W80211_CR_34> { enum { STEPS = 6, NV = 2 }; };
-template <> struct Body<W80211_CR_56> { enum { STEPS = 10, NV = 3 }; };
-
-/* one body = STEPS trellis steps fed by NV float4 loads; survivors for step pair k go to dst[k*32] */
-template <int CR>
-__device__ __forceinline__ void body(float (&m)[64], float (&n)[64], const float4* v, uint4* dst)
-{
-    if (CR == W80211_CR_12) {
-        acs2<MASK_FULL, MASK_FULL>(m, n, v[0].x, v[0].y, v[0].z, v[0].w, dst);
-        acs2<MASK_FULL, MASK_FULL>(m, n, v[1].x, v[1].y, v[1].z, v[1].w, dst + 32);
-    } else if (CR == W80211_CR_23) { /* {1,1},{1,0} */
-        acs2<MASK_FULL, MASK_A>(m, n, v[0].x, v[0].y, v[0].z, 0.f, dst);
-        acs2<MASK_FULL, MASK_A>(m, n, v[0].w, v[1].x, v[1].y, 0.f, dst + 32);
-        acs2<MASK_FULL, MASK_A>(m, n, v[1].z, v[1].w, v[2].x, 0.f, dst + 64);
-        acs2<MASK_FULL, MASK_A>(m, n, v[2].y, v[2].z, v[2].w, 0.f, dst + 96);
-    } else if (CR == W80211_CR_34) { /* {1,1},{1,0},{0,1} */
-        acs2<MASK_FULL, MASK_A>(m, n, v[0].x, v[0].y, v[0].z, 0.f, dst);
-        acs2<MASK_B, MASK_FULL>(m, n, 0.f, v[0].w, v[1].x, v[1].y, dst + 32);
-        acs2<MASK_A, MASK_B>(m, n, v[1].z, 0.f, 0.f, v[1].w, dst + 64);
-    } else { /* 5/6: {1,1},{1,0},{0,1},{1,0},{0,1} */
-        acs2<MASK_FULL, MASK_A>(m, n, v[0].x, v[0].y, v[0].z, 0.f, dst);
-        acs2<MASK_B, MASK_A>(m, n, 0.f, v[0].w, v[1].x, 0.f, dst + 32);
-        acs2<MASK_B, MASK_FULL>(m, n, 0.f, v[1].y, v[1].z, v[1].w, dst + 64);
-        acs2<MASK_A, MASK_B>(m, n, v[2].x, 0.f, 0.f, v[2].y, dst + 96);
-        acs2<MASK_A, MASK_B>(m, n, v[2].z, 0.f, 0.f, v[2].w, dst + 128);
-    }
 }
 
 /* ---- in-place variant.  A butterfly reads states (2b, 2b+1) and writes states (b, b+32); writing the
@@ -241,58 +190,116 @@ __device__ __forceinline__ void viterbi_run6(const float* __restrict__ llr, int 
     tail_ip<4>(m, t, trellis, ph, period, q, surv2);
 }
 
-/* grp[g] = {x: first survivor row (even), y: rows reserved (even, >= max trellis in the group),
- *           z: first bit-word row, w: code rate of the group} */
-template <int CR>
-__device__ __forceinline__ void viterbi_run(const float* __restrict__ llr, int trellis, uint4* __restrict__ surv4 /* + lane */)
-{
-    enum { STEPS = Body<CR>::STEPS, NV = Body<CR>::NV };
-    const float NEG = -1000000000000000.0f; /* sentinel of vstb_init (decode_impl.cc:174-177) */
-    float m[64], n[64];
-#pragma unroll
-    for (int i = 0; i < 64; i++) m[i] = NEG;
-    m[0] = 0.0f;
+/* ---- in-place body of any whole number of puncturing periods.  After STEPS steps state x sits in register
+ * rol6(x, STEPS mod 6); one permutation of the 64 registers closes the map (free in SASS: ptxas gives the last step's
+ * results the registers the loop head expects).  This is what lets rate 5/6 (period 5, which does not divide 6) run in
+ * place, and what lets every rate use a loop body that fits the instruction cache.  Numbers:
+ * profiles/experiments/r2_viterbi_body_length.txt. */
+template <int CR> __host__ __device__ constexpr int vit_period() { return CR == W80211_CR_12 ? 1 : (CR == W80211_CR_23 ? 2 : (CR == W80211_CR_34 ? 3 : 5)); }
+__host__ __device__ constexpr int vit_mask_of(int k) { return k == 0 ? MASK_FULL : ((k & 1) ? MASK_A : MASK_B); } /* {1,1},{1,0},{0,1},{1,0},{0,1} */
+__host__ __device__ constexpr int vit_llrs_before(int k) { return k == 0 ? 0 : k + 1; }                           /* inside one period */
 
-    const int nbody = trellis / STEPS;
-    const float4* src = reinterpret_cast<const float4*>(llr);
-    float4 cur[NV], nxt[NV];
-    if (nbody > 0) {
-#pragma unroll
-        for (int k = 0; k < NV; k++) cur[k] = __ldg(src + k);
+template <int CR, int K>
+__device__ __forceinline__ void ip_step(float (&m)[64], const float* v, uint2* base, int par)
+{
+    constexpr int PER = vit_period<CR>(), ph = K % PER, MASK = vit_mask_of(ph);
+    constexpr int i0 = (K / PER) * (PER + 1) + vit_llrs_before(ph);
+    const float t0 = MASK == MASK_B ? 0.f : v[i0];
+    const float t1 = MASK == MASK_A ? 0.f : v[MASK == MASK_FULL ? i0 + 1 : i0];
+    uint2 w;
+    acs_ip<K % 6, MASK>(m, t0, t1, w.x, w.y);
+    const int k = par + K; /* survivors: one uint4 per step pair and lane = two uint2, rows of 32 lanes */
+    base[(size_t)(k >> 1) * 64 + (k & 1)] = w;
+}
+
+template <int CR, int K0, int N>
+struct IpUnroll {
+    static __device__ __forceinline__ void run(float (&m)[64], const float* v, uint2* base, int par)
+    {
+        ip_step<CR, K0>(m, v, base, par);
+        IpUnroll<CR, K0 + 1, N - 1>::run(m, v, base, par);
     }
-    for (int b = 0; b < nbody; b++) {
-        if (b + 1 < nbody) {
+};
+template <int CR, int K0>
+struct IpUnroll<CR, K0, 0> {
+    static __device__ __forceinline__ void run(float (&)[64], const float*, uint2*, int) {}
+};
+
+template <int NF>
+__device__ __forceinline__ void ip_load(const float* __restrict__ llr, int b, float* v)
+{
+    /* body b starts at float b * NF of a 16-byte aligned packet */
+    if (NF % 4 == 0) {
+        const float4* src = reinterpret_cast<const float4*>(llr) + (size_t)b * (NF / 4);
 #pragma unroll
-            for (int k = 0; k < NV; k++) nxt[k] = __ldg(src + (size_t)(b + 1) * NV + k);
+        for (int k = 0; k < NF / 4; k++) {
+            const float4 x = __ldg(src + k);
+            v[4 * k] = x.x, v[4 * k + 1] = x.y, v[4 * k + 2] = x.z, v[4 * k + 3] = x.w;
         }
-        body<CR>(m, n, cur, surv4 + (size_t)b * (STEPS / 2) * 32);
+    } else if (NF % 2 == 0) {
+        const float2* src = reinterpret_cast<const float2*>(llr) + (size_t)b * (NF / 2);
 #pragma unroll
-        for (int k = 0; k < NV; k++) cur[k] = nxt[k];
-    }
-    /* tail: fewer than STEPS steps left; same arithmetic through the full-step template with an
-     * explicit 0.0f for a punctured position (x + 0.0f == x) */
-    int t = nbody * STEPS;
-    if (t < trellis) {
-        const int period = CR == W80211_CR_12 ? 1 : (CR == W80211_CR_23 ? 2 : (CR == W80211_CR_34 ? 3 : 5));
-        const float* q = llr + (size_t)nbody * NV * 4;
-        uint2* surv2 = reinterpret_cast<uint2*>(surv4);
-        int ph = 0;
-        for (; t < trellis; t++) {
-            /* puncture pattern pairs (A present, B present): phase 0 {1,1}; odd phases {1,0}; even > 0 {0,1} */
-            bool hasA = ph == 0 || (ph & 1), hasB = ph == 0 || !(ph & 1);
-            float t0 = 0.0f, t1 = 0.0f;
-            if (hasA) t0 = __ldg(q++);
-            if (hasB) t1 = __ldg(q++);
-            uint2 w;
-            acs<MASK_FULL>(m, n, t0, t1, w.x, w.y);
-#pragma unroll
-            for (int i = 0; i < 64; i++) m[i] = n[i];
-            surv2[((size_t)(t >> 1) * 32) * 2 + (t & 1)] = w;
-            if (++ph >= period) ph = 0;
+        for (int k = 0; k < NF / 2; k++) {
+            const float2 x = __ldg(src + k);
+            v[2 * k] = x.x, v[2 * k + 1] = x.y;
         }
+    } else {
+        const float* src = llr + (size_t)b * NF;
+#pragma unroll
+        for (int k = 0; k < NF; k++) v[k] = __ldg(src + k);
     }
 }
 
+template <int CR, int STEPS>
+__device__ __forceinline__ void viterbi_run_ip(const float* __restrict__ llr, int trellis, uint4* __restrict__ surv4)
+{
+    constexpr int PER = vit_period<CR>(), NF = STEPS / PER * (PER + 1);
+    static_assert(STEPS % PER == 0 && STEPS >= 1 && STEPS <= 12, "a body is a whole number of puncturing periods");
+    const float NEG = -1000000000000000.0f; /* sentinel of vstb_init (decode_impl.cc:174-177) */
+    float m[64];
+#pragma unroll
+    for (int i = 0; i < 64; i++) m[i] = NEG;
+    m[0] = 0.0f;
+    const int nbody = trellis / STEPS;
+    uint2* surv2 = reinterpret_cast<uint2*>(surv4);
+    float cur[NF], nxt[NF];
+#pragma unroll
+    for (int k = 0; k < NF; k++) cur[k] = 0.f;
+    if (nbody > 0) ip_load<NF>(llr, 0, cur);
+    constexpr int PFD = VIT_PF * 6 / STEPS; /* prefetch distance in bodies: about 48 steps ahead */
+    for (int b = 0; b < nbody; b++) {
+        ip_load<NF>(llr, b + 1 < nbody ? b + 1 : b, nxt);
+        if (b + PFD < nbody) asm volatile("prefetch.global.L2 [%0];" ::"l"(llr + (size_t)(b + PFD) * NF));
+        const int t0 = STEPS * b;
+        IpUnroll<CR, 0, STEPS>::run(m, cur, surv2 + (size_t)(t0 >> 1) * 64, t0 & 1);
+        if (STEPS % 6 != 0) {
+            float n[64];
+#pragma unroll
+            for (int x = 0; x < 64; x++) n[x] = m[rol6(x, STEPS % 6)];
+#pragma unroll
+            for (int x = 0; x < 64; x++) m[x] = n[x];
+        }
+#pragma unroll
+        for (int k = 0; k < NF; k++) cur[k] = nxt[k];
+    }
+    /* tail: fewer than STEPS steps; the map is the identity here, an absent LLR is an explicit 0.0f as in the reference */
+    int t = nbody * STEPS, ph = 0;
+    const float* q = llr + (size_t)nbody * NF;
+    tail_ip<0>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 2) tail_ip<1>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 3) tail_ip<2>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 4) tail_ip<3>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 5) tail_ip<4>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 6) tail_ip<5>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 7) tail_ip<0>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 8) tail_ip<1>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 9) tail_ip<2>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 10) tail_ip<3>(m, t, trellis, ph, PER, q, surv2);
+    if (STEPS > 11) tail_ip<4>(m, t, trellis, ph, PER, q, surv2);
+}
+
+/* grp[g] = {x: first survivor row (even), y: rows reserved (even, >= max trellis in the group),
+ *           z: first bit-word row, w: code rate of the group} */
 /* one kernel per code rate (groups are sorted by rate), so each gets its own register allocation */
 template <int CR>
 __global__ void __launch_bounds__(32, VIT_MINBLK) viterbi_kernel(const int4* __restrict__ grp, const int* __restrict__ slot_pkt,
@@ -306,12 +313,11 @@ __global__ void __launch_bounds__(32, VIT_MINBLK) viterbi_kernel(const int4* __r
     const int trellis = desc[pkt].trellis;
     const float* l = llr + desc[pkt].llr_off;
     uint4* s4 = reinterpret_cast<uint4*>(surv + (size_t)G.x * 32) + lane;
-#if VIT_INPLACE
-    if (CR == W80211_CR_12 || CR == W80211_CR_34 || CR == W80211_CR_23)
+    constexpr int STEPS = CR == W80211_CR_12 ? VIT_STEPS_12 : (CR == W80211_CR_23 ? VIT_STEPS_23 : (CR == W80211_CR_34 ? VIT_STEPS_34 : VIT_STEPS_56));
+    if (STEPS == 6 && CR != W80211_CR_56)
         viterbi_run6<CR>(l, trellis, s4);
     else
-#endif
-        viterbi_run<CR>(l, trellis, s4);
+        viterbi_run_ip<CR, STEPS>(l, trellis, s4);
 }
 
 /* vstb_end (decode_impl.cc:282-302): traceback from state 0 at the end of the trellis.  One thread
