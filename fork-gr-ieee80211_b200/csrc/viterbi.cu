@@ -754,3 +754,206 @@ int w_launch_traceback(cudaStream_t st, const int* cr_first, const int4* grp, co
     }
     return launches;
 }
+
+/* =====================================================================================================
+ * w80211_viterbi_noalloc(): LLRs -> decoded trellis bits for callers that cannot allocate (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree / allocating routine: inputs and outputs are the caller's device
+ * buffers, the packet table travels as a kernel argument, and the survivor words -- the scratch memory of the Viterbi
+ * forward pass -- live in the file-scope array below, which every GPU that loads this library holds until exit
+ * (W80211_NOALLOC_MAX_PKTS x 32784 x 8 B = 4.0 MiB).  The kernels are variants of viterbi_warp_kernel /
+ * traceback_warp_kernel above (same device functions, same arithmetic, so the same bits as every other path); the
+ * existing kernels and entry points are untouched.
+ *
+ * In host code `g_na_surv` is only a stand-in for the symbol, not a device address: the address is taken once per device,
+ * with that device current, by cudaGetSymbolAddress() and handed to the kernels as an argument.
+ * Every call shares the array.  Nothing in it has to start at zero: the forward kernel writes every survivor word the
+ * traceback kernel uses (steps 0 .. trellis-1 of each packet) before it runs, on the same stream; words left over from an
+ * earlier call lie beyond `trellis` and are never used.  Calls that overlap on the GPU (different streams, or several
+ * host threads) race on the array: serialise them. */
+#define NA_STRIDE 32784 /* survivor words reserved per packet: W80211_T_MAX rounded up to a step pair */
+static __device__ __align__(256) uint2 g_na_surv[(size_t)W80211_NOALLOC_MAX_PKTS * NA_STRIDE];
+
+struct NaParams {
+    w80211_noalloc_pkt pk[W80211_NOALLOC_MAX_PKTS];
+};
+
+template <int CR>
+__global__ void __launch_bounds__(32, WV_MINBLK) viterbi_warp_na_kernel(const NaParams P, const float* __restrict__ llr, uint2* __restrict__ surv)
+{
+    enum { STEPS = WvBody<CR>::STEPS, NF = WvBody<CR>::NF };
+    const int p = blockIdx.x, lane = threadIdx.x;
+    if (P.pk[p].cr != CR) return; /* one launch per code rate present, every block looks at its own packet */
+    const int trellis = P.pk[p].trellis;
+    const float* __restrict__ l = llr + P.pk[p].llr_off;
+    uint2* __restrict__ s = surv + (size_t)p * NA_STRIDE;
+    WvLane W;
+    wv_setup(lane, W);
+    const float NEG = -1000000000000000.0f;
+    float x0 = lane == 0 ? 0.0f : NEG, x1 = NEG;
+    const bool store = lane == 0;
+    const int nbody = trellis / STEPS;
+    float cur[NF], nxt[NF];
+#pragma unroll
+    for (int k = 0; k < NF; k++) cur[k] = 0.f;
+    if (nbody > 0) wv_load<CR>(l, 0, cur);
+    for (int b = 0; b < nbody; b++) {
+        wv_load<CR>(l, b + 1 < nbody ? b + 1 : b, nxt);
+        WvUnroll<CR, 0, STEPS>::run(x0, x1, cur, W, s + (size_t)b * STEPS, store);
+#pragma unroll
+        for (int k = 0; k < NF; k++) cur[k] = nxt[k];
+    }
+    const int period = wv_period<CR>();
+    const float* q = l + (size_t)nbody * NF;
+    int ph = 0;
+    for (int t = nbody * STEPS; t < trellis; t++) {
+        const bool hasA = ph == 0 || (ph & 1), hasB = ph == 0 || !(ph & 1);
+        float t0 = 0.0f, t1 = 0.0f;
+        if (hasA) t0 = __ldg(q++);
+        if (hasB) t1 = __ldg(q++);
+        const uint2 w = wv_step_rt(t % 5, x0, x1, t0, t1, W);
+        if (store) s[t] = w;
+        if (++ph >= period) ph = 0;
+    }
+}
+
+/* traceback_warp_kernel with the packet table by value and packet-contiguous output words */
+__global__ void __launch_bounds__(32, 16) traceback_warp_na_kernel(const NaParams P, const uint2* __restrict__ surv, uint32_t* __restrict__ bits)
+{
+    const int p = blockIdx.x, lane = threadIdx.x;
+    const int T = P.pk[p].trellis;
+    const uint2* __restrict__ s = surv + (size_t)p * NA_STRIDE;
+    uint32_t* __restrict__ out = bits + P.pk[p].bits_off;
+    const int W = max(((T + 1023) >> 10) << 5, 256);
+    const int lo = lane * W, hi = lo + W;
+    uint32_t s0 = hi >= T ? 1u : 0xffffffffu, s1 = hi >= T ? 0u : 0xffffffffu;
+    TbPos pos = {0u, 0u};
+    uint32_t word = 0;
+    int m = 0;
+    bool merged = false;
+    while (m < W) {
+        tb_block16<true>(s, hi - m - 16, T, pos, s0, s1, word);
+        tb_block16<true>(s, hi - m - 32, T, pos, s0, s1, word);
+        m += 32;
+        merged = __popc(s0) + __popc(s1) == 1;
+        if (__all_sync(WV_FULL, merged)) break;
+    }
+    if (__all_sync(WV_FULL, merged)) {
+        pos.r = s1 ? 1u : 0u;
+        pos.l = (uint32_t)__ffs((int)(s0 | s1)) - 1u;
+        for (int t = hi - m - 32; t >= lo; t -= 32) {
+            word = 0;
+            tb_block16<false>(s, t + 16, T, pos, s0, s1, word);
+            tb_block16<false>(s, t, T, pos, s0, s1, word);
+            if (t < T) out[t >> 5] = word;
+        }
+        uint32_t el = __shfl_down_sync(WV_FULL, pos.l, 1), er = __shfl_down_sync(WV_FULL, pos.r, 1);
+        if (lane == 31) el = er = 0u;
+        pos.l = el;
+        pos.r = er;
+        for (int t = hi - 32; t >= hi - m; t -= 32) {
+            word = 0;
+            tb_block16<false>(s, t + 16, T, pos, s0, s1, word);
+            tb_block16<false>(s, t, T, pos, s0, s1, word);
+            if (t < T) out[t >> 5] = word;
+        }
+    } else if (lane == 0) {
+        pos.l = pos.r = 0u;
+        for (int t = ((T - 1) >> 5) << 5; t >= 0; t -= 32) {
+            word = 0;
+            tb_block16<false>(s, t + 16, T, pos, s0, s1, word);
+            tb_block16<false>(s, t, T, pos, s0, s1, word);
+            out[t >> 5] = word;
+        }
+    }
+}
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+namespace {
+enum { NA_MAX_DEVICES = 64 };
+std::mutex g_na_mutex;
+uint2* g_na_ptr[NA_MAX_DEVICES]; /* device address of g_na_surv on each device, taken at that device's first call */
+
+int na_fail(char* err, size_t errlen, int code, const char* fmt, ...)
+{
+    if (err && errlen) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, errlen, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+/* LLRs a packet's trellis consumes (depuncturing of decode_impl.cc:210-229): phase 0 of a period takes two, later phases one */
+long long na_llr_needed(int trellis, int cr)
+{
+    static const int per[4] = {1, 2, 3, 5};
+    const long long full = trellis / per[cr], rem = trellis % per[cr];
+    return full * (per[cr] + 1) + (rem > 0 ? rem + 1 : 0);
+}
+} // namespace
+
+extern "C" int w80211_viterbi_noalloc(int32_t device, void* stream, int32_t npkt, const w80211_noalloc_pkt* pkts, const float* llr,
+                                      uint64_t nllr, uint32_t* bits, uint64_t nwords, char* err, size_t errlen)
+{
+    if (err && errlen) err[0] = 0;
+    if (npkt < 0 || (npkt > 0 && (!pkts || !llr || !bits)))
+        return na_fail(err, errlen, W80211_E_ARG, "w80211_viterbi_noalloc: npkt %d with a missing pkts / llr / bits pointer", npkt);
+    if (npkt > W80211_NOALLOC_MAX_PKTS)
+        return na_fail(err, errlen, W80211_E_CAPACITY,
+                       "w80211_viterbi_noalloc: %d packets in one call, the static scratch holds %d (W80211_NOALLOC_MAX_PKTS); split the call or use "
+                       "w80211_decode_batch", npkt, W80211_NOALLOC_MAX_PKTS);
+    if (device < 0 || device >= NA_MAX_DEVICES) return na_fail(err, errlen, W80211_E_ARG, "w80211_viterbi_noalloc: device %d out of range", device);
+    if (((uintptr_t)llr & 15u) != 0) return na_fail(err, errlen, W80211_E_ARG, "w80211_viterbi_noalloc: llr must be 16-byte aligned");
+    NaParams P;
+    memset(&P, 0, sizeof(P));
+    int present = 0;
+    for (int p = 0; p < npkt; p++) {
+        const w80211_noalloc_pkt& k = pkts[p];
+        if (k.cr < 0 || k.cr > 3) return na_fail(err, errlen, W80211_E_ARG, "w80211_viterbi_noalloc: packet %d: code rate %d not in 0..3", p, k.cr);
+        if (k.trellis < 1 || k.trellis > W80211_T_MAX)
+            return na_fail(err, errlen, W80211_E_CAPACITY, "w80211_viterbi_noalloc: packet %d: trellis %d outside 1..%d (the scratch reserves %d survivor words per packet)",
+                           p, k.trellis, W80211_T_MAX, NA_STRIDE);
+        if ((k.llr_off & 3u) != 0) return na_fail(err, errlen, W80211_E_ARG, "w80211_viterbi_noalloc: packet %d: llr_off must be a multiple of 4 floats", p);
+        if (k.llr_off > nllr || (uint64_t)na_llr_needed(k.trellis, k.cr) > nllr - k.llr_off)
+            return na_fail(err, errlen, W80211_E_ARG, "w80211_viterbi_noalloc: packet %d: %lld LLRs from %llu do not fit in %llu", p,
+                           na_llr_needed(k.trellis, k.cr), (unsigned long long)k.llr_off, (unsigned long long)nllr);
+        if (k.bits_off > nwords || (uint64_t)((k.trellis + 31) >> 5) > nwords - k.bits_off)
+            return na_fail(err, errlen, W80211_E_ARG, "w80211_viterbi_noalloc: packet %d: %d output words from %llu do not fit in %llu", p,
+                           (k.trellis + 31) >> 5, (unsigned long long)k.bits_off, (unsigned long long)nwords);
+        P.pk[p] = k;
+        present |= 1 << k.cr;
+    }
+    if (npkt == 0) return W80211_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return na_fail(err, errlen, W80211_E_CUDA, "w80211_viterbi_noalloc: cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    uint2* surv = nullptr;
+    {
+        /* once per device, with that device current: the symbol's address on THIS device */
+        std::lock_guard<std::mutex> lock(g_na_mutex);
+        if (!g_na_ptr[device]) {
+            void* ptr = nullptr;
+            e = cudaGetSymbolAddress(&ptr, g_na_surv);
+            if (e != cudaSuccess || !ptr) {
+                cudaGetLastError();
+                return na_fail(err, errlen, W80211_E_CUDA, "w80211_viterbi_noalloc: cudaGetSymbolAddress on device %d: %s", device, cudaGetErrorString(e));
+            }
+            g_na_ptr[device] = static_cast<uint2*>(ptr);
+        }
+        surv = g_na_ptr[device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (present & 1) viterbi_warp_na_kernel<W80211_CR_12><<<npkt, 32, 0, st>>>(P, llr, surv);
+    if (present & 2) viterbi_warp_na_kernel<W80211_CR_23><<<npkt, 32, 0, st>>>(P, llr, surv);
+    if (present & 4) viterbi_warp_na_kernel<W80211_CR_34><<<npkt, 32, 0, st>>>(P, llr, surv);
+    if (present & 8) viterbi_warp_na_kernel<W80211_CR_56><<<npkt, 32, 0, st>>>(P, llr, surv);
+    traceback_warp_na_kernel<<<npkt, 32, 0, st>>>(P, surv, bits);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return na_fail(err, errlen, W80211_E_CUDA, "w80211_viterbi_noalloc: kernel launch: %s", cudaGetErrorString(e));
+    return W80211_OK;
+}

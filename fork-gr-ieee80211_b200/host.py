@@ -20,7 +20,7 @@ SYMBOLS = [
     "w80211_abi_version", "w80211_sizeof", "w80211_create", "w80211_destroy", "w80211_last_error", "w80211_stats_get",
     "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
     "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free", "w80211_signal_batch",
-    "w80211_detect_batch", "w80211_presiso_batch",
+    "w80211_detect_batch", "w80211_presiso_batch", "w80211_viterbi_noalloc",
 ]
 
 
@@ -93,6 +93,10 @@ class DetectOut(C.Structure):
                 ("next", C.c_uint64), ("syncs", C.c_void_p), ("state", DetectState)]
 
 
+NOALLOC_MAX_PKTS = 16
+NOALLOC_PKT_DTYPE = np.dtype([("llr_off", "<u8"), ("bits_off", "<u8"), ("trellis", "<i4"), ("cr", "<i4")], align=True)
+
+
 class Stats(C.Structure):
     _fields_ = [("packets_in", C.c_uint64), ("packets_decoded", C.c_uint64), ("dropped_gate", C.c_uint64),
                 ("ndp", C.c_uint64), ("unsupported", C.c_uint64), ("bad_input", C.c_uint64),
@@ -138,6 +142,7 @@ def load():
         L.w80211_signal_batch.argtypes = [vp, C.POINTER(SignalIn), C.POINTER(SignalOut)]
         L.w80211_detect_batch.argtypes = [vp, C.POINTER(DetectIn), C.POINTER(DetectOut)]
         L.w80211_presiso_batch.argtypes = [vp, vp, C.c_uint64, C.c_int32, vp, vp]
+        L.w80211_viterbi_noalloc.argtypes = [C.c_int32, vp, C.c_int32, vp, vp, C.c_uint64, vp, C.c_uint64, C.c_char_p, C.c_size_t]
         _lib = L
     return _lib
 

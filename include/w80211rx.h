@@ -320,6 +320,30 @@ int w80211_rx_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w8021
 int w80211_rx_collect(w80211_ctx* ctx, int slot);
 int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out);
 
+/* ---- no-allocation decode (no counterpart in the reference) -----------
+ * LLRs -> decoded trellis bits (what vstb_update + vstb_end leave in v_scramBits, lib/decode_impl.cc:205-302: still scrambled,
+ * bit i of word j = trellis bit 32 j + i) for callers that cannot call cudaMalloc: code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid allocation.  The call allocates nothing (no cudaMalloc / cudaFree, no library
+ * routine that allocates) and needs no w80211_ctx: llr and bits are the caller's device buffers on `device`, `stream` is the
+ * caller's cudaStream_t (NULL = the default stream), pkts is a host array that travels as a kernel argument.  The survivor
+ * words of the Viterbi forward pass live in a static device array inside the library, W80211_NOALLOC_MAX_PKTS x 32784 x 8 B
+ * = 4.0 MiB, held by every GPU that loads the library until the process exits; hence the limits: at most
+ * W80211_NOALLOC_MAX_PKTS packets per call (more: W80211_E_CAPACITY and a message in err), trellis <= W80211_T_MAX.
+ * The kernels are enqueued on `stream` and the call returns without waiting.  All calls share the static array, which
+ * keeps the last call's contents (nothing in it has to start at zero: every word that is read was written by the same
+ * call first): calls that overlap on the GPU -- other streams, other threads -- race; serialise them on one stream.
+ * Same arithmetic as w80211_decode_batch, so the bits are identical to what it decodes (tests/test_zz_no_alloc.py). */
+#define W80211_NOALLOC_MAX_PKTS 16
+typedef struct w80211_noalloc_pkt {
+    uint64_t llr_off;  /* index of the packet's first LLR in llr[], a multiple of 4 (llr itself 16-byte aligned) */
+    uint64_t bits_off; /* index of the packet's first output word in bits[]; (trellis + 31) / 32 words are written */
+    int32_t trellis;   /* tag "trellis", 1 .. W80211_T_MAX */
+    int32_t cr;        /* tag "cr", W80211_CR_12 .. W80211_CR_56; the packet's LLRs are punctured accordingly */
+} w80211_noalloc_pkt;
+/* err (may be NULL): receives a message when the return value is not W80211_OK */
+int w80211_viterbi_noalloc(int32_t device, void* stream, int32_t npkt, const w80211_noalloc_pkt* pkts, const float* llr,
+                           uint64_t nllr, uint32_t* bits, uint64_t nwords, char* err, size_t errlen);
+
 #ifdef __cplusplus
 }
 #endif
