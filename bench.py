@@ -745,7 +745,8 @@ def signal_leg(torch, host, rx, wl, bo_d, dev, nsm, K):
 
 
 def blocks_leg(args):
-    """The GNU Radio block path: placeholder until the harness leg is wired in (see tools/blocks_bench.py)."""
+    """The GNU Radio block path (gr/lib demod -> decode streamed by the mock scheduler's chain runner over fc32 items in host
+    memory) beside the reference's blocks under the same runner: tools/blocks_bench.py."""
     try:
         import tools.blocks_bench as bb
     except Exception:

@@ -28,7 +28,9 @@
 #include <new>
 #include <string>
 #include <deque>
+#include <mutex>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 #include "common.cuh"
 
@@ -72,6 +74,9 @@ struct Slot {
     uint32_t mpdu_cap = 0;   /* records the device / pinned buffers of this batch can hold */
     uint32_t mpdu_eager = 0; /* records copied to the host together with the counters */
     uint8_t* post_bytes = nullptr; /* where the post kernel writes PSDU bytes (the caller's device buffer or s.bytes) */
+    const float* llr_src = nullptr; /* LLRs the Viterbi kernels read: s.llr.p, the caller's device buffer, or a lease's */
+    uint64_t lease = 0;             /* lease this batch reads (decode_submit with W80211_MEM_LEASE), released by collect */
+    std::vector<uint64_t> v_src_off; /* decode_batch: the caller's own LLR offsets, handed back with the descriptors */
     uint32_t launches = 0;
     w80211_batch_out* out = nullptr;
     std::vector<uint32_t> h_psdu_off;
@@ -109,6 +114,9 @@ struct w80211_ctx {
     cudaStream_t cstream = nullptr;
     cudaEvent_t last_tail = nullptr; /* EV_POST of the batch whose decode was enqueued last (see enqueue_front) */
     W80211Tables* d_tab = nullptr;
+    /* LLR buffers this context has handed out as leases come back here when they retire (under g_lease_mu) */
+    std::vector<DevBuf> llr_free;
+    std::deque<uint64_t> leases; /* handles exported by this context, oldest first */
     Slot slots[4];
     SigStage sig;
     w80211_stats stats = {};
@@ -172,6 +180,69 @@ int pin_reserve(w80211_ctx* ctx, PinBuf& b, size_t bytes)
         int r_ = (call);    \
         if (r_ < 0) return r_; \
     } while (0)
+
+/* ---- LLR leases: a demod batch's LLR buffer, detached from its slot so that another context on the same GPU can decode
+ * from it (w80211rx.h).  One process-wide table; every access under g_lease_mu.  The buffer of a retired lease goes back
+ * to its producer's free list (or is freed when the producer is gone), never to cudaFree on the hot path: cudaFree
+ * synchronises the device. */
+struct Lease {
+    int device = 0;
+    DevBuf buf;
+    uint64_t nfloats = 0;
+    w80211_ctx* owner = nullptr; /* nullptr: the producer has been destroyed */
+    int readers = 0;             /* decode batches in flight that read it */
+    bool retired = false;        /* no longer valid for new readers; freed when readers drops to 0 */
+};
+std::mutex g_lease_mu;
+std::unordered_map<uint64_t, Lease> g_leases;
+uint64_t g_lease_next = 1;
+int g_lease_consumers = 0;
+
+/* g_lease_mu held */
+void lease_free_locked(uint64_t id)
+{
+    auto it = g_leases.find(id);
+    if (it == g_leases.end()) return;
+    Lease& L = it->second;
+    if (L.owner)
+        L.owner->llr_free.push_back(L.buf);
+    else if (L.buf.p) {
+        int cur = -1;
+        cudaGetDevice(&cur);
+        cudaSetDevice(L.device);
+        cudaFree(L.buf.p);
+        if (cur >= 0) cudaSetDevice(cur);
+    }
+    g_leases.erase(it);
+}
+
+/* the slot's LLR buffer, at least `bytes`: kept, or taken from the context's free list, or allocated */
+int llr_reserve(w80211_ctx* ctx, Slot& s, size_t bytes)
+{
+    if (bytes <= s.llr.cap) return 0;
+    {
+        std::lock_guard<std::mutex> lk(g_lease_mu);
+        int best = -1;
+        for (int i = 0; i < (int)ctx->llr_free.size(); i++)
+            if (ctx->llr_free[i].cap >= bytes && (best < 0 || ctx->llr_free[i].cap < ctx->llr_free[best].cap)) best = i;
+        if (best >= 0) {
+            if (s.llr.p) ctx->llr_free.push_back(s.llr);
+            s.llr = ctx->llr_free[best];
+            ctx->llr_free.erase(ctx->llr_free.begin() + best);
+            return 0;
+        }
+    }
+    return dev_reserve(ctx, s.llr, bytes);
+}
+
+void lease_release(uint64_t id)
+{
+    if (!id) return;
+    std::lock_guard<std::mutex> lk(g_lease_mu);
+    auto it = g_leases.find(id);
+    if (it == g_leases.end()) return;
+    if (--it->second.readers <= 0 && it->second.retired) lease_free_locked(id);
+}
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -269,7 +340,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
 
     /* device buffers */
     RS(dev_reserve(ctx, s.symprefix, (size_t)(npkt + 1) * 4));
-    if (assign_llr) RS(dev_reserve(ctx, s.llr, (size_t)(s.n_llr + 64) * 4));
+    if (assign_llr) RS(llr_reserve(ctx, s, (size_t)(s.n_llr + 64) * 4));
     if (do_decode) {
         RS(dev_reserve(ctx, s.surv, (size_t)row * 32 * 8 + 1024));
         RS(dev_reserve(ctx, s.bits, (size_t)wrow * 32 * 4 + 1024));
@@ -333,7 +404,7 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
         if (ctx->vit_mode == W80211_CFG_VITERBI_WARP || (ctx->vit_mode == W80211_CFG_VITERBI_AUTO && npk < ctx->warp_max_pkts)) warp_mask |= 1 << cr;
     }
     int nvit = w_launch_viterbi(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
-                                (const float*)s.llr.p, (uint2*)s.surv.p, warp_mask);
+                                s.llr_src ? s.llr_src : (const float*)s.llr.p, (uint2*)s.surv.p, warp_mask);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_VIT], st));
     nvit += w_launch_traceback(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
@@ -422,6 +493,8 @@ int enqueue_input_header(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w8
     s.did_demod = true;
     s.did_decode = do_decode;
     s.launches = 0;
+    s.llr_src = nullptr;
+    s.lease = 0;
     s.in_host = in->mem == W80211_MEM_HOST;
     out->n_mpdu = out->n_crc_ok = 0;
     out->n_bytes = out->n_llr = out->psdu_bits_ok = 0;
@@ -557,6 +630,10 @@ int collect_slot(w80211_ctx* ctx, Slot& s)
     CK(cudaStreamSynchronize(s.stream));
     const auto tc0 = std::chrono::steady_clock::now();
     s.busy = false;
+    if (s.lease) {
+        lease_release(s.lease);
+        s.lease = 0;
+    }
     w80211_batch_out* out = s.out;
     const w80211_desc* hd = (const w80211_desc*)s.h_desc.p;
     out->n_llr = s.n_llr;
@@ -722,6 +799,7 @@ size_t w80211_sizeof(int what)
     case 11: return sizeof(w80211_detect_state);
     case 12: return sizeof(w80211_detect_in);
     case 13: return sizeof(w80211_detect_out);
+    case 14: return sizeof(w80211_decode_in);
     default: return 0;
     }
 }
@@ -800,6 +878,22 @@ void w80211_destroy(w80211_ctx* ctx)
             if (e) cudaEventDestroy(e);
         if (g.stream) cudaStreamDestroy(g.stream);
     }
+    {
+        /* leases this context produced: those nobody reads are freed now, the others when their reader collects */
+        std::lock_guard<std::mutex> lk(g_lease_mu);
+        for (uint64_t id : ctx->leases) {
+            auto it = g_leases.find(id);
+            if (it == g_leases.end()) continue;
+            it->second.owner = nullptr;
+            it->second.retired = true;
+            if (it->second.readers <= 0) lease_free_locked(id);
+        }
+        ctx->leases.clear();
+        for (DevBuf& b : ctx->llr_free)
+            if (b.p) cudaFree(b.p);
+        ctx->llr_free.clear();
+    }
+    for (int i = 0; i < 4; i++) lease_release(ctx->slots[i].lease);
     if (ctx->cstream) cudaStreamDestroy(ctx->cstream);
     if (ctx->origin) cudaEventDestroy(ctx->origin);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
@@ -880,6 +974,8 @@ int w80211_rx_collect(w80211_ctx* ctx, int slot)
         cudaStreamSynchronize(s.stream);
         s.busy = false;
         s.phase = 0;
+        lease_release(s.lease);
+        s.lease = 0;
         return s.cont_err;
     }
     int r = collect_slot(ctx, s);
@@ -892,6 +988,89 @@ int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out
     int r = w80211_rx_submit(ctx, 0, in, out);
     if (r < 0) return r;
     return w80211_rx_collect(ctx, 0);
+}
+
+int w80211_rx_poll(w80211_ctx* ctx, int slot)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
+    Slot& s = ctx->slots[slot];
+    if (!s.busy) return fail(ctx, W80211_E_STATE, "slot idle: nothing to poll");
+    CK(cudaSetDevice(ctx->device));
+    progress(ctx, -1);
+    if (s.phase != 2) return 0;
+    if (s.cont_err < 0) return 1; /* collect will report it */
+    const cudaError_t q = cudaStreamQuery(s.stream);
+    if (q == cudaErrorNotReady) return 0;
+    if (q != cudaSuccess) return fail(ctx, W80211_E_CUDA, "slot %d: %s", slot, cudaGetErrorString(q));
+    return 1;
+}
+
+int w80211_demod_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w80211_batch_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
+    Slot& s = ctx->slots[slot];
+    progress(ctx, -1);
+    int r = enqueue_input_header(ctx, s, in, out, false);
+    if (r < 0) {
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        return r;
+    }
+    s.busy = true;
+    s.phase = 1;
+    s.cont_err = 0;
+    ctx->pending.push_back(slot);
+    return W80211_OK;
+}
+
+int w80211_llr_export(w80211_ctx* ctx, int slot, uint64_t* handle)
+{
+    if (!ctx || !handle) return W80211_E_ARG;
+    *handle = 0;
+    if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
+    Slot& s = ctx->slots[slot];
+    if (s.busy || !s.did_demod) return fail(ctx, W80211_E_STATE, "llr_export: slot %d holds no collected demod batch", slot);
+    if (!s.llr.p || s.n_llr == 0) return fail(ctx, W80211_E_STATE, "llr_export: the batch in slot %d produced no LLRs", slot);
+    std::lock_guard<std::mutex> lk(g_lease_mu);
+    /* keep the newest W80211_LEASES_KEPT - 1 and this one; older ones retire (a decode batch still reading one keeps its
+     * memory alive until it collects) */
+    while ((int)ctx->leases.size() >= W80211_LEASES_KEPT) {
+        const uint64_t old = ctx->leases.front();
+        ctx->leases.pop_front();
+        auto it = g_leases.find(old);
+        if (it == g_leases.end()) continue;
+        it->second.retired = true;
+        if (it->second.readers <= 0) lease_free_locked(old);
+    }
+    const uint64_t id = g_lease_next++;
+    Lease& L = g_leases[id];
+    L.device = ctx->device;
+    L.buf = s.llr;
+    L.nfloats = s.n_llr;
+    L.owner = ctx;
+    s.llr = DevBuf();
+    s.n_llr = 0;
+    ctx->leases.push_back(id);
+    *handle = id;
+    return W80211_OK;
+}
+
+int w80211_llr_query(uint64_t handle, int32_t* device, uint64_t* nfloats)
+{
+    std::lock_guard<std::mutex> lk(g_lease_mu);
+    auto it = g_leases.find(handle);
+    if (it == g_leases.end() || it->second.retired) return W80211_E_STATE;
+    if (device) *device = it->second.device;
+    if (nfloats) *nfloats = it->second.nfloats;
+    return W80211_OK;
+}
+
+int w80211_lease_consumers(int delta)
+{
+    std::lock_guard<std::mutex> lk(g_lease_mu);
+    g_lease_consumers = std::max(0, g_lease_consumers + delta);
+    return g_lease_consumers;
 }
 
 int w80211_presiso_batch(w80211_ctx* ctx, const float* sig, uint64_t nsamples, int32_t mem, float* preac, float* preconj)
@@ -1282,67 +1461,131 @@ int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_
     return collect_slot(ctx, s);
 }
 
-int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, const float* llr, uint64_t nllr,
-                        int32_t llr_mem, w80211_batch_out* out)
+/* LLRs + descriptors -> everything of the decode half enqueued on the slot's stream; does not wait */
+static int decode_submit_impl(w80211_ctx* ctx, int slot, const w80211_decode_in* in, w80211_batch_out* out)
 {
-    if (!ctx) return W80211_E_ARG;
-    if (npkt < 0 || !out || (npkt > 0 && (!desc || !llr))) return fail(ctx, W80211_E_ARG, "bad decode_batch arguments");
-    Slot& s = ctx->slots[0];
-    if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy");
+    if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
+    if (!in || !out || in->npkt < 0 || (in->npkt > 0 && !in->desc) || in->llr_mem < W80211_MEM_HOST || in->llr_mem > W80211_MEM_LEASE ||
+        (in->npkt > 0 && in->llr_mem != W80211_MEM_LEASE && !in->llr))
+        return fail(ctx, W80211_E_ARG, "bad decode arguments");
+    Slot& s = ctx->slots[slot];
+    if (s.busy) return fail(ctx, W80211_E_STATE, "slot busy: collect it first");
     CK(cudaSetDevice(ctx->device));
-    progress(ctx, -2);
+    progress(ctx, -1);
     cudaStream_t st = s.stream;
+    const int npkt = in->npkt;
+    const int llr_mem = in->llr_mem;
+    const float* llr = in->llr;
+    uint64_t nllr = in->nllr;
     s.npkt = npkt;
     s.out = out;
     s.did_demod = false;
     s.did_decode = true;
+    s.in_host = llr_mem == W80211_MEM_HOST;
     s.launches = 0;
+    s.llr_src = nullptr;
+    s.lease = 0;
     out->n_mpdu = out->n_crc_ok = 0;
     out->n_bytes = out->n_llr = out->psdu_bits_ok = 0;
-    CK(cudaEventRecord(s.ev[EV_START], st));
-    RS(pin_reserve(ctx, s.h_desc, (size_t)npkt * sizeof(w80211_desc) + 16));
-    RS(dev_reserve(ctx, s.desc, (size_t)npkt * sizeof(w80211_desc) + 16));
+    if (llr_mem == W80211_MEM_LEASE) {
+        std::lock_guard<std::mutex> lk(g_lease_mu);
+        auto it = g_leases.find(in->lease);
+        if (it == g_leases.end() || it->second.retired) return fail(ctx, W80211_E_STATE, "decode: LLR lease %llu has been retired", (unsigned long long)in->lease);
+        if (it->second.device != ctx->device)
+            return fail(ctx, W80211_E_ARG, "decode: LLR lease lives on device %d, this context on %d", it->second.device, ctx->device);
+        it->second.readers++;
+        s.lease = in->lease;
+        llr = (const float*)it->second.buf.p;
+        nllr = it->second.nfloats;
+    }
+    auto bail = [&](int r) {
+        lease_release(s.lease);
+        s.lease = 0;
+        return r;
+    };
+#define CKB(call)                                                                                                       \
+    do {                                                                                                                \
+        cudaError_t e_ = (call);                                                                                        \
+        if (e_ != cudaSuccess) return bail(fail(ctx, W80211_E_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_))); \
+    } while (0)
+#define RSB(call)                  \
+    do {                           \
+        int r_ = (call);           \
+        if (r_ < 0) return bail(r_); \
+    } while (0)
+    CKB(cudaEventRecord(s.ev[EV_START], st));
+    RSB(pin_reserve(ctx, s.h_desc, (size_t)npkt * sizeof(w80211_desc) + 16));
+    RSB(dev_reserve(ctx, s.desc, (size_t)npkt * sizeof(w80211_desc) + 16));
     w80211_desc* hd = (w80211_desc*)s.h_desc.p;
     if (llr_mem == W80211_MEM_DEVICE) {
-        if (npkt) CK(cudaMemcpy(hd, desc, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost));
+        if (npkt) CKB(cudaMemcpy(hd, in->desc, (size_t)npkt * sizeof(w80211_desc), cudaMemcpyDeviceToHost));
     } else if (npkt) {
-        memcpy(hd, desc, (size_t)npkt * sizeof(w80211_desc));
+        memcpy(hd, in->desc, (size_t)npkt * sizeof(w80211_desc));
     }
-    /* LLRs into the slot's buffer at 16-byte aligned offsets */
-    uint64_t off = 0;
-    std::vector<uint64_t> src_off(npkt);
+    std::vector<uint64_t>& src_off = s.v_src_off;
+    src_off.resize((size_t)npkt);
+    /* The kernels need every packet's LLRs at a 16-byte aligned offset.  A caller that already laid them out that way
+     * (gr/lib/decode_impl.cc, a lease, the LLR stream demod_batch returned) is decoded from where they are -- device
+     * memory and leases without any copy, host memory with one copy of the whole range; anything else is repacked packet
+     * by packet into the slot's buffer. */
+    bool in_place = true;
+    uint64_t lo = ~0ull, hi = 0;
     for (int p = 0; p < npkt; p++) {
         w80211_desc& d = hd[p];
-        src_off[p] = (uint64_t)d.llr_off;
-        if (d.status == W80211_ST_OK && d.total > 0 && d.llr_off >= 0 && (uint64_t)d.llr_off + (uint64_t)d.total <= nllr) {
-            d.llr_off = (int64_t)off;
-            off += align_up((size_t)d.total, 4) + 16;
-        } else {
+        src_off[(size_t)p] = (uint64_t)d.llr_off;
+        const bool ok = d.status == W80211_ST_OK && d.total > 0 && d.llr_off >= 0 && (uint64_t)d.llr_off + (uint64_t)d.total <= nllr;
+        if (!ok) {
             if (d.status == W80211_ST_OK) d.status = W80211_ST_BAD_INPUT;
             d.llr_off = -1;
+            continue;
+        }
+        if (d.llr_off & 3) in_place = false;
+        lo = std::min(lo, (uint64_t)d.llr_off);
+        hi = std::max(hi, (uint64_t)d.llr_off + (uint64_t)d.total);
+    }
+    if (((uintptr_t)llr & 15u) != 0) in_place = false;
+    if (llr_mem == W80211_MEM_LEASE && !in_place) return bail(fail(ctx, W80211_E_ARG, "decode: lease offsets must be multiples of 4"));
+    if (lo > hi) lo = hi = 0;
+    if (in_place && llr_mem != W80211_MEM_HOST) {
+        s.llr_src = llr;
+        s.n_llr = 0;
+    } else if (in_place) {
+        lo &= ~(uint64_t)3;
+        RSB(llr_reserve(ctx, s, (size_t)(hi - lo + 64) * 4));
+        if (hi > lo) CKB(cudaMemcpyAsync(s.llr.p, llr + lo, (size_t)(hi - lo) * 4, cudaMemcpyHostToDevice, st));
+        for (int p = 0; p < npkt; p++)
+            if (hd[p].llr_off >= 0) hd[p].llr_off -= (int64_t)lo;
+        s.n_llr = hi - lo;
+    } else {
+        uint64_t off = 0;
+        for (int p = 0; p < npkt; p++) {
+            w80211_desc& d = hd[p];
+            if (d.llr_off < 0) continue;
+            d.llr_off = (int64_t)off;
+            off += align_up((size_t)d.total, 4) + 16;
+        }
+        s.n_llr = off;
+        RSB(llr_reserve(ctx, s, (size_t)(off + 64) * 4));
+        for (int p = 0; p < npkt; p++) {
+            const w80211_desc& d = hd[p];
+            if (d.llr_off < 0) continue;
+            CKB(cudaMemcpyAsync((float*)s.llr.p + d.llr_off, llr + src_off[(size_t)p], (size_t)d.total * 4,
+                                llr_mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
         }
     }
-    s.n_llr = off;
-    RS(dev_reserve(ctx, s.llr, (size_t)(off + 64) * 4));
-    for (int p = 0; p < npkt; p++) {
-        const w80211_desc& d = hd[p];
-        if (d.llr_off < 0) continue;
-        CK(cudaMemcpyAsync((float*)s.llr.p + d.llr_off, llr + src_off[p], (size_t)d.total * 4,
-                           llr_mem == W80211_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
-    }
-    CK(cudaEventRecord(s.ev[EV_H2D], st));
-    CK(cudaEventRecord(s.ev[EV_HDR], st));
-    int r = plan_and_upload(ctx, s, hd, false, true);
-    if (r < 0) return r;
-    CK(cudaEventRecord(s.ev[EV_PLAN], st));
-    CK(cudaEventRecord(s.ev[EV_DEMOD], st));
-    s.busy = true;
-    r = enqueue_decode_tail(ctx, s);
+    CKB(cudaEventRecord(s.ev[EV_H2D], st));
+    CKB(cudaEventRecord(s.ev[EV_HDR], st));
+    const auto tp0 = std::chrono::steady_clock::now();
+    RSB(plan_and_upload(ctx, s, hd, false, true));
+    s.host_plan_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tp0).count();
+    CKB(cudaEventRecord(s.ev[EV_PLAN], st));
+    CKB(cudaEventRecord(s.ev[EV_DEMOD], st));
+    int r = enqueue_decode_tail(ctx, s);
     if (r == 0) {
-        /* hand back descriptors with the caller's own LLR offsets */
-        bool want = out->want_llr;
-        out->want_llr = 0;
+        /* the descriptors go back with the caller's own LLR offsets (decode_batch, after collect) */
+        const bool want = out->want_llr;
         w80211_desc* user_desc = out->desc;
+        out->want_llr = 0;
         out->desc = nullptr;
         r = finish_outputs(ctx, s);
         out->want_llr = want;
@@ -1350,14 +1593,44 @@ int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, 
     }
     if (r < 0) {
         cudaStreamSynchronize(s.stream);
-        s.busy = false;
-        return r;
+        return bail(r);
     }
-    r = collect_slot(ctx, s);
+#undef CKB
+#undef RSB
+    s.busy = true;
+    s.phase = 2;
+    s.cont_err = 0;
+    return W80211_OK;
+}
+
+int w80211_decode_submit(w80211_ctx* ctx, int slot, const w80211_decode_in* in, w80211_batch_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    return decode_submit_impl(ctx, slot, in, out);
+}
+
+int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, const float* llr, uint64_t nllr,
+                        int32_t llr_mem, w80211_batch_out* out)
+{
+    if (!ctx) return W80211_E_ARG;
+    if (llr_mem != W80211_MEM_HOST && llr_mem != W80211_MEM_DEVICE) return fail(ctx, W80211_E_ARG, "bad decode_batch arguments");
+    progress(ctx, -2);
+    w80211_decode_in in;
+    memset(&in, 0, sizeof(in));
+    in.npkt = npkt;
+    in.llr_mem = llr_mem;
+    in.desc = desc;
+    in.llr = llr;
+    in.nllr = nllr;
+    int r = decode_submit_impl(ctx, 0, &in, out);
+    if (r < 0) return r;
+    r = w80211_rx_collect(ctx, 0);
     if (r == 0 && out->desc && out->mem == W80211_MEM_HOST) {
+        const Slot& s = ctx->slots[0];
+        const w80211_desc* hd = (const w80211_desc*)s.h_desc.p;
         for (int p = 0; p < npkt; p++) {
             out->desc[p] = hd[p];
-            out->desc[p].llr_off = (int64_t)src_off[p];
+            out->desc[p].llr_off = (int64_t)s.v_src_off[(size_t)p];
         }
     }
     return r;

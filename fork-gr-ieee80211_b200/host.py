@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libw80211rx.so")  # the product library; bench.py --resident-only --lib points tuning runs at a variant build
 
-MEM_HOST, MEM_DEVICE = 0, 1
+MEM_HOST, MEM_DEVICE, MEM_LEASE = 0, 1, 2
 ST_OK, ST_DROP_GATE, ST_NDP, ST_UNSUPPORTED, ST_BAD_INPUT = 0, 1, 2, 3, 4
 F_L, F_HT, F_VHT = 0, 1, 2
 
@@ -20,7 +20,8 @@ SYMBOLS = [
     "w80211_abi_version", "w80211_sizeof", "w80211_create", "w80211_destroy", "w80211_last_error", "w80211_stats_get",
     "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
     "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free", "w80211_signal_batch",
-    "w80211_detect_batch", "w80211_presiso_batch", "w80211_viterbi_noalloc",
+    "w80211_detect_batch", "w80211_presiso_batch", "w80211_viterbi_noalloc", "w80211_rx_poll", "w80211_demod_submit",
+    "w80211_decode_submit", "w80211_llr_export", "w80211_llr_query", "w80211_lease_consumers",
 ]
 
 
@@ -60,6 +61,11 @@ class BatchOut(C.Structure):
                 ("mpdu_capacity", C.c_uint32), ("llr", C.c_void_p), ("llr_capacity", C.c_uint64),
                 ("n_mpdu", C.c_uint32), ("n_crc_ok", C.c_uint32), ("n_bytes", C.c_uint64), ("n_llr", C.c_uint64),
                 ("psdu_bits_ok", C.c_uint64)]
+
+
+class DecodeIn(C.Structure):
+    _fields_ = [("npkt", C.c_int32), ("llr_mem", C.c_int32), ("desc", C.c_void_p), ("llr", C.c_void_p), ("nllr", C.c_uint64),
+                ("lease", C.c_uint64)]
 
 
 SYNC_TAGGED = 1
@@ -143,6 +149,12 @@ def load():
         L.w80211_detect_batch.argtypes = [vp, C.POINTER(DetectIn), C.POINTER(DetectOut)]
         L.w80211_presiso_batch.argtypes = [vp, vp, C.c_uint64, C.c_int32, vp, vp]
         L.w80211_viterbi_noalloc.argtypes = [C.c_int32, vp, C.c_int32, vp, vp, C.c_uint64, vp, C.c_uint64, C.c_char_p, C.c_size_t]
+        L.w80211_rx_poll.argtypes = [vp, C.c_int]
+        L.w80211_demod_submit.argtypes = [vp, C.c_int, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+        L.w80211_decode_submit.argtypes = [vp, C.c_int, C.POINTER(DecodeIn), C.POINTER(BatchOut)]
+        L.w80211_llr_export.argtypes = [vp, C.c_int, C.POINTER(C.c_uint64)]
+        L.w80211_llr_query.argtypes = [C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_uint64)]
+        L.w80211_lease_consumers.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -354,6 +366,50 @@ class Receiver:
         self._check(self.L.w80211_decode_batch(self.h, npkt, desc.ctypes.data, llr.ctypes.data, llr.size, MEM_HOST,
                                                C.byref(bo)))
         return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo)
+
+    def demod_submit(self, slot, iq, pkts, chan, want_llr=True, mu_pos=0):
+        """IQ -> LLRs + descriptors on slot `slot` without waiting (w80211_demod_submit); collect(slot) returns the Result."""
+        bcap, mcap, lcap = self._caps(iq, pkts)
+        bi = self.make_in(iq, pkts, chan, mu_pos=mu_pos)
+        bo, arrs = self.make_out_host(len(pkts), 16, 1, lcap if want_llr else 0)
+        keep = (bi, bo, arrs, iq, pkts, chan)
+        self._check(self.L.w80211_demod_submit(self.h, slot, C.byref(bi), C.byref(bo)))
+        self._keep[slot] = keep
+
+    def poll(self, slot):
+        r = self.L.w80211_rx_poll(self.h, slot)
+        if r < 0:
+            self._check(r)
+        return bool(r)
+
+    def llr_export(self, slot):
+        """Detach the LLRs of the demod batch last collected from `slot` as a lease (w80211_llr_export); returns the handle."""
+        h = C.c_uint64(0)
+        self._check(self.L.w80211_llr_export(self.h, slot, C.byref(h)))
+        return int(h.value)
+
+    def llr_query(self, handle):
+        dev, n = C.c_int32(-1), C.c_uint64(0)
+        r = self.L.w80211_llr_query(int(handle), C.byref(dev), C.byref(n))
+        return None if r != 0 else (int(dev.value), int(n.value))
+
+    def decode_submit(self, slot, desc, llr=None, lease=0):
+        """Descriptors + LLRs (host array, or a lease handle) -> bytes on slot `slot` without waiting (w80211_decode_submit)."""
+        desc = np.ascontiguousarray(desc, DESC_DTYPE)
+        npkt = len(desc)
+        di = DecodeIn()
+        di.npkt, di.desc = npkt, desc.ctypes.data
+        if lease:
+            di.llr_mem, di.lease = MEM_LEASE, int(lease)
+        else:
+            llr = np.ascontiguousarray(llr, np.float32)
+            di.llr_mem, di.llr, di.nllr = MEM_HOST, llr.ctypes.data, llr.size
+        bcap = int(np.maximum(desc["trellis"], 0).astype(np.int64).sum()) // 8 + 64 * npkt + 64
+        bo, arrs = self.make_out_host(npkt, bcap, npkt * 2 + bcap // 32 + 64)
+        arrs["desc"][:] = desc
+        keep = (di, bo, arrs, desc, llr)
+        self._check(self.L.w80211_decode_submit(self.h, slot, C.byref(di), C.byref(bo)))
+        self._keep[slot] = keep
 
     def signal(self, raw, pos, rad=0.0, snr=0.0, rssi=0.0, start=0, final=True, tagged=None):
         """Raw samples + sync flags -> packets in demod's input format (w80211_signal_batch): what signal / signal2 do.

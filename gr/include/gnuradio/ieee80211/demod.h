@@ -18,8 +18,9 @@ class IEEE80211_API demod : virtual public gr::block
 {
 public:
     typedef std::shared_ptr<demod> sptr;
-    /* mupos / mugid: MU-MIMO user position and group id of the reference block; the MU path is out of
-     * scope here, the arguments are kept so flowgraphs build unchanged. */
+    /* mupos / mugid: MU-MIMO user position and group id of the reference block.  mupos (0 or 1) selects this
+     * receiver's stream of a VHT MU PPDU (lib/demod_impl.cc:347-379); mugid is kept for the
+     * signature only, the reference never reads it either. */
     static sptr make(int mupos, int mugid);
 };
 

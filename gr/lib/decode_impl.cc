@@ -1,5 +1,5 @@
 /* decode_impl.cc -- decoder block: stream and message protocol of the reference
- * (lib/decode_impl.cc:33-162), batch decode on the GPU through w80211_decode_batch(). */
+ * (lib/decode_impl.cc:33-162), batches decoded on the GPU through w80211_decode_submit() without waiting. */
 #include "decode_impl.h"
 
 #include <algorithm>
@@ -21,22 +21,33 @@ decode_impl::decode_impl(bool ifdebug)
       d_env(rx_env::read()),
       d_ctx(nullptr),
       d_failed(false),
-      d_fill(0),
-      d_ncomplete(0),
+      d_cur(-1),
+      d_partial_in(-1),
       d_left(0),
       d_copy_left(0),
+      d_lost_leases(0),
+      d_trace(std::getenv("W80211_TRACE") != nullptr),
+      d_t_ingest(0),
+      d_t_submit(0),
+      d_t_wait(0),
+      d_t_publish(0),
+      d_n_work(0),
+      d_n_batches(0),
+      d_n_pkts(0),
+      d_n_leased(0),
       d_nPktCorrect(0)
 {
     message_port_register_out(pmt::mp("out"));
     std::memset(d_legacyMcsCount, 0, sizeof(d_legacyMcsCount));
     std::memset(d_htMcsCount, 0, sizeof(d_htMcsCount));
     std::memset(d_vhtMcsCount, 0, sizeof(d_vhtMcsCount));
+    for (bool& b : d_slot_busy) b = false;
     set_tag_propagation_policy(block::TPP_DONT);
     w80211_cfg cfg;
     std::memset(&cfg, 0, sizeof(cfg));
     cfg.device = d_env.device;
     cfg.max_packets = d_env.max_batch;
-    cfg.nslots = 1;
+    cfg.nslots = NSLOTS;
     int r = w80211_abi_version() == W80211_ABI_VERSION ? w80211_create(&cfg, &d_ctx) : W80211_E_ARG;
     if (w80211_abi_version() != W80211_ABI_VERSION)
         std::fprintf(stderr, "ieee80211 %s: libw80211rx.so has ABI version %d, this block was built for %d\n", "decode",
@@ -48,28 +59,79 @@ decode_impl::decode_impl(bool ifdebug)
                      "ieee80211 decode: w80211_create failed (%d): no usable CUDA device %d; there is no CPU path, "
                      "packets will be dropped\n",
                      r, d_env.device);
+    } else {
+        w80211_lease_consumers(+1); /* demod blocks of this process may leave their LLRs in HBM from now on */
     }
+    take_free_set();
 }
 
 decode_impl::~decode_impl()
 {
-    if (d_ctx) w80211_destroy(d_ctx);
+    if (d_trace)
+        std::fprintf(stderr, "ieee80211 decode trace: %llu general_work calls, %llu batches, %llu packets (%llu from LLR leases, %llu lost "
+                             "leases); ingest %.1f ms, submit %.1f ms, waiting for the GPU %.1f ms, publish %.1f ms\n",
+                     (unsigned long long)d_n_work, (unsigned long long)d_n_batches, (unsigned long long)d_n_pkts, (unsigned long long)d_n_leased,
+                     (unsigned long long)d_lost_leases, 1e3 * d_t_ingest, 1e3 * d_t_submit, 1e3 * d_t_wait, 1e3 * d_t_publish);
+    if (d_ctx) {
+        w80211_lease_consumers(-1);
+        for (int idx : d_queue)
+            if (d_sets[idx].state == SET_INFLIGHT) w80211_rx_collect(d_ctx, d_sets[idx].slot);
+        w80211_destroy(d_ctx);
+    }
 }
 
 void decode_impl::forecast(int /*noutput_items*/, gr_vector_int& ninput_items_required)
 {
-    ninput_items_required[0] = d_ncomplete > 0 ? 0 : 1;
+    const bool pending = !d_queue.empty() || (d_cur >= 0 && d_sets[d_cur].ncomplete > 0);
+    ninput_items_required[0] = pending ? 0 : 1;
+}
+
+bool decode_impl::take_free_set()
+{
+    if (d_cur >= 0) return true;
+    int idx = -1;
+    for (int i = 0; i < NSETS; i++)
+        if (d_sets[i].state == SET_FREE) {
+            idx = i;
+            break;
+        }
+    if (idx < 0) return false;
+    batch_set& b = d_sets[idx];
+    b.state = SET_FILLING;
+    b.desc.clear();
+    b.fill = 0;
+    b.ncomplete = 0;
+    b.lease = 0;
+    if (d_partial_in >= 0) {
+        /* the packet that was still arriving when that set was submitted: its LLRs so far move over */
+        batch_set& src = d_sets[d_partial_in];
+        w80211_desc last = src.desc.back();
+        const uint64_t have = src.fill - (uint64_t)last.llr_off;
+        if (b.llr.reserve((size_t)last.total + 64, 0)) {
+            if (have) std::memcpy(b.llr.data(), src.llr.data() + last.llr_off, (size_t)have * sizeof(float));
+        } else {
+            if (!d_failed) std::fprintf(stderr, "ieee80211 decode: out of host memory for staging, dropping packets\n");
+            d_failed = true;
+        }
+        last.llr_off = 0;
+        b.desc.push_back(last);
+        b.fill = have;
+        d_partial_in = -1;
+    }
+    d_cur = idx;
+    return true;
 }
 
 /* Tags on the first LLR of a packet, keys and defaults as at decode_impl.cc:70-89, gates as at :93-121. */
-bool decode_impl::start_packet(uint64_t abs_offset)
+int decode_impl::start_packet(uint64_t abs_offset)
 {
     std::vector<gr::tag_t> tags;
     get_tags_in_range(tags, 0, abs_offset, abs_offset + 1);
-    if (tags.empty()) return false;
+    if (tags.empty()) return START_NONE;
     w80211_desc d;
     std::memset(&d, 0, sizeof(d));
     long format = 99999, len = 99999, total = 99999, cr = 99999, mcs = 99999, ampdu = 99999, trellis = 99999;
+    long lease_tag = 0, lease_off = -1, nohost = 0;
     pmt::pmt_t ndp_chan = pmt::PMT_NIL;
     for (const auto& t : tags) {
         const std::string key = pmt::symbol_to_string(t.key);
@@ -86,15 +148,24 @@ bool decode_impl::start_packet(uint64_t abs_offset)
         else if (key == "sssnr0") d.sssnr0 = (float)pmt::to_float(t.value);
         else if (key == "sssnr1") d.sssnr1 = (float)pmt::to_float(t.value);
         else if (key == "mu2x1chan") ndp_chan = t.value;
+        else if (key == "w80211_llr") lease_tag = pmt::to_long(t.value);
+        else if (key == "w80211_off") lease_off = pmt::to_long(t.value);
+        else if (key == "w80211_nohost") nohost = pmt::to_long(t.value);
     }
-    if (total <= 0) return false; /* malformed stream: nothing to skip over */
-    d_left = total;
-    d_copy_left = 0;
-    if (len > W80211_B_MAX || trellis > W80211_T_MAX) return true; /* skipped by the reference, decode_impl.cc:93-97 */
+    if (total <= 0) return START_NONE; /* malformed stream: nothing to skip over */
+    if (len > W80211_B_MAX || trellis > W80211_T_MAX) { /* skipped by the reference, decode_impl.cc:93-97 */
+        d_left = total;
+        d_copy_left = 0;
+        return START_OK;
+    }
     if (trellis == 0) {
         /* VHT NDP: forward the 2x1 channel of the tag as [20, len lo, len hi, 256 floats] (decode_impl.cc:100-121).
-         * Earlier packets are decoded first so the publication order stays the arrival order. */
-        if (d_ncomplete > 0) run_batch();
+         * Every earlier packet is decoded and published first so the publication order stays the arrival order. */
+        if (d_sets[d_cur].ncomplete > 0) submit_current();
+        drain_all();
+        if (!take_free_set()) return START_LATER;
+        d_left = total;
+        d_copy_left = 0;
         std::vector<std::complex<float>> ch;
         if (!pmt::is_null(ndp_chan)) ch = pmt::c32vector_elements(ndp_chan);
         const int nbytes = 256 * (int)sizeof(float);
@@ -109,9 +180,37 @@ bool decode_impl::start_packet(uint64_t abs_offset)
         }
         pmt::pmt_t meta = pmt::dict_add(pmt::make_dict(), pmt::mp("len"), pmt::from_long(nbytes + 3));
         message_port_pub(pmt::mp("out"), pmt::cons(meta, pmt::make_blob(d_msg.data(), d_msg.size())));
-        return true;
+        return START_OK;
     }
-    if (trellis < 0 || cr < 0 || cr > 3 || len < 0) return true; /* cannot be decoded; skip its LLRs */
+    if (trellis < 0 || cr < 0 || cr > 3 || len < 0) { /* cannot be decoded; skip its LLRs */
+        d_left = total;
+        d_copy_left = 0;
+        return START_OK;
+    }
+    /* where this packet's LLRs are: a lease of this repo's demod (still valid, on this GPU), or the stream items */
+    uint64_t src = 0;
+    if (lease_tag > 0 && lease_off >= 0 && (lease_off & 3) == 0 && !d_failed) {
+        int32_t dev = -1;
+        uint64_t nf = 0;
+        if (w80211_llr_query((uint64_t)lease_tag, &dev, &nf) == W80211_OK && dev == d_env.device && (uint64_t)lease_off + (uint64_t)total <= nf)
+            src = (uint64_t)lease_tag;
+    }
+    if (!src && nohost) {
+        /* the items were never written and the lease is gone (this block fell more than W80211_LEASES_KEPT batches behind) */
+        if (d_lost_leases++ == 0)
+            std::fprintf(stderr, "ieee80211 decode: a packet's LLRs were left on the GPU (W80211_LLR_HANDOFF=device) and their lease has "
+                                 "been retired; packet dropped (further ones are counted silently)\n");
+        d_left = total;
+        d_copy_left = 0;
+        return START_OK;
+    }
+    if (!d_sets[d_cur].desc.empty() && d_sets[d_cur].lease != src) {
+        /* one source per batch */
+        submit_current();
+        if (d_cur < 0) return START_LATER;
+    }
+    batch_set& b = d_sets[d_cur];
+    b.lease = src;
     d.status = W80211_ST_OK;
     d.format = (int32_t)format;
     d.mcs = (int32_t)mcs;
@@ -120,17 +219,26 @@ bool decode_impl::start_packet(uint64_t abs_offset)
     d.ampdu = (int32_t)ampdu;
     d.trellis = (int32_t)trellis;
     d.total = (int32_t)total;
-    d.llr_off = (int64_t)((d_fill + 3) & ~(uint64_t)3); /* 16-byte aligned: no repacking inside the library */
-    if (!d_llr.reserve((size_t)d.llr_off + (size_t)total + 64, (size_t)d_fill)) {
+    d_left = total;
+    if (b.ncomplete == 0) b.oldest = std::chrono::steady_clock::now();
+    if (src) {
+        d.llr_off = (int64_t)lease_off;
+        d_copy_left = 0;
+        b.desc.push_back(d);
+        b.ncomplete++;
+        return START_OK;
+    }
+    d.llr_off = (int64_t)((b.fill + 3) & ~(uint64_t)3); /* 16-byte aligned: decoded from where it is staged */
+    if (!b.llr.reserve((size_t)d.llr_off + (size_t)total + 64, (size_t)b.fill)) {
         if (!d_failed) std::fprintf(stderr, "ieee80211 decode: out of host memory for staging, dropping packets\n");
         d_failed = true;
-        return true;
+        d_copy_left = 0;
+        return START_OK;
     }
-    d_fill = (uint64_t)d.llr_off;
+    b.fill = (uint64_t)d.llr_off;
     d_copy_left = total;
-    if (d_ncomplete == 0) d_oldest = std::chrono::steady_clock::now();
-    d_desc.push_back(d);
-    return true;
+    b.desc.push_back(d);
+    return START_OK;
 }
 
 void decode_impl::debug_line(const w80211_desc& d, bool crc_ok)
@@ -186,52 +294,127 @@ void decode_impl::publish(const w80211_desc& d, const uint8_t* mpdu, uint32_t le
     message_port_pub(pmt::mp("out"), pmt::cons(meta, pmt::make_blob(d_msg.data(), d_msg.size())));
 }
 
-void decode_impl::run_batch()
+/* The whole packets of the set being filled go to the GPU; returns without waiting for them. */
+void decode_impl::submit_current()
 {
-    const int npkt = d_ncomplete;
-    const bool partial = (int)d_desc.size() > npkt; /* the packet still arriving stays staged */
+    const double t_in = d_trace ? trace_now() : 0.0;
+    struct at_exit {
+        decode_impl* c;
+        double t;
+        ~at_exit()
+        {
+            if (c->d_trace) c->d_t_submit += trace_now() - t;
+        }
+    } guard{ this, t_in };
+    d_n_batches++;
+    d_n_pkts += (uint64_t)d_sets[d_cur].ncomplete;
+    if (d_sets[d_cur].lease) d_n_leased += (uint64_t)d_sets[d_cur].ncomplete;
+    const int idx = d_cur;
+    batch_set& b = d_sets[idx];
+    const int npkt = b.ncomplete;
+    const bool partial = (int)b.desc.size() > npkt; /* the packet still arriving moves to the next set */
+    b.npkt = npkt;
+    b.ok = false;
+    b.slot = -1;
+    bool sent = false;
     if (!d_failed && npkt > 0) {
+        int slot = -1;
+        for (;;) {
+            for (int s = 0; s < NSLOTS; s++)
+                if (!d_slot_busy[s]) slot = s;
+            if (slot >= 0 || d_queue.empty()) break;
+            finish_front(true); /* both slots are busy: the oldest batch is collected and published first */
+        }
         size_t bytes_cap = 64, mpdu_cap = 64;
         for (int p = 0; p < npkt; p++) {
-            bytes_cap += (size_t)((d_desc[(size_t)p].trellis + 7) / 8 + 8 + 15) & ~(size_t)15;
-            mpdu_cap += (size_t)d_desc[(size_t)p].trellis / 32 + 1; /* one A-MPDU delimiter per 32 bits at most */
+            bytes_cap += (size_t)((b.desc[(size_t)p].trellis + 7) / 8 + 8 + 15) & ~(size_t)15;
+            mpdu_cap += (size_t)b.desc[(size_t)p].trellis / 32 + 1; /* one A-MPDU delimiter per 32 bits at most */
         }
-        d_psdu_off.assign((size_t)npkt, 0);
-        if (d_bytes.reserve(bytes_cap, 0) && d_mpdus.reserve(mpdu_cap * sizeof(w80211_mpdu), 0)) {
-            w80211_batch_out out;
-            std::memset(&out, 0, sizeof(out));
-            out.mem = W80211_MEM_HOST;
-            out.bytes = d_bytes.data();
-            out.bytes_capacity = d_bytes.capacity();
-            out.psdu_off = d_psdu_off.data();
-            out.mpdus = reinterpret_cast<w80211_mpdu*>(d_mpdus.data());
-            out.mpdu_capacity = (uint32_t)std::min<size_t>(d_mpdus.capacity() / sizeof(w80211_mpdu), 0xffffffffu);
-            uint64_t nllr = d_fill;
-            if (partial) nllr = (uint64_t)d_desc[(size_t)npkt].llr_off;
-            int r = w80211_decode_batch(d_ctx, npkt, d_desc.data(), d_llr.data(), nllr, W80211_MEM_HOST, &out);
-            if (r != W80211_OK) {
-                std::fprintf(stderr, "ieee80211 decode: w80211_decode_batch: %s; batch dropped\n", w80211_last_error(d_ctx));
+        b.psdu_off.assign((size_t)npkt, 0);
+        if (slot < 0) {
+            std::fprintf(stderr, "ieee80211 decode: no free GPU slot, batch dropped\n");
+        } else if (b.bytes.reserve(bytes_cap, 0) && b.mpdus.reserve(mpdu_cap * sizeof(w80211_mpdu), 0)) {
+            std::memset(&b.out, 0, sizeof(b.out));
+            b.out.mem = W80211_MEM_HOST;
+            b.out.bytes = b.bytes.data();
+            b.out.bytes_capacity = b.bytes.capacity();
+            b.out.psdu_off = b.psdu_off.data();
+            b.out.mpdus = reinterpret_cast<w80211_mpdu*>(b.mpdus.data());
+            b.out.mpdu_capacity = (uint32_t)std::min<size_t>(b.mpdus.capacity() / sizeof(w80211_mpdu), 0xffffffffu);
+            std::memset(&b.in, 0, sizeof(b.in));
+            b.in.npkt = npkt;
+            b.in.desc = b.desc.data();
+            if (b.lease) {
+                b.in.llr_mem = W80211_MEM_LEASE;
+                b.in.lease = b.lease;
             } else {
-                const w80211_mpdu* m = out.mpdus;
-                for (uint32_t i = 0; i < out.n_mpdu; i++)
-                    publish(d_desc[m[i].pkt], d_bytes.data() + m[i].off, m[i].len, m[i].crc_ok != 0);
+                b.in.llr_mem = W80211_MEM_HOST;
+                b.in.llr = b.llr.data();
+                b.in.nllr = partial ? (uint64_t)b.desc[(size_t)npkt].llr_off : b.fill;
+            }
+            if (w80211_decode_submit(d_ctx, slot, &b.in, &b.out) == W80211_OK) {
+                b.slot = slot;
+                d_slot_busy[slot] = true;
+                sent = true;
+            } else {
+                std::fprintf(stderr, "ieee80211 decode: w80211_decode_submit: %s; batch dropped\n", w80211_last_error(d_ctx));
             }
         } else {
             std::fprintf(stderr, "ieee80211 decode: out of host memory for the results, batch dropped\n");
         }
     }
-    if (partial) {
-        w80211_desc last = d_desc.back();
-        const uint64_t have = d_fill - (uint64_t)last.llr_off;
-        if (have) std::memmove(d_llr.data(), d_llr.data() + last.llr_off, (size_t)have * sizeof(float));
-        last.llr_off = 0;
-        d_desc.assign(1, last);
-        d_fill = have;
-    } else {
-        d_desc.clear();
-        d_fill = 0;
+    b.state = sent ? SET_INFLIGHT : SET_READY;
+    d_queue.push_back(idx);
+    d_cur = -1;
+    if (partial) d_partial_in = idx;
+    take_free_set();
+}
+
+/* The oldest submitted batch: collected (waiting for it if asked to), its frames published, its set freed. */
+bool decode_impl::finish_front(bool wait)
+{
+    if (d_queue.empty()) return false;
+    const int idx = d_queue.front();
+    batch_set& b = d_sets[idx];
+    if (b.state == SET_INFLIGHT) {
+        if (!wait && w80211_rx_poll(d_ctx, b.slot) == 0) return false;
+        const double t_w = d_trace ? trace_now() : 0.0;
+        const int r = w80211_rx_collect(d_ctx, b.slot);
+        if (d_trace) d_t_wait += trace_now() - t_w;
+        d_slot_busy[b.slot] = false;
+        b.ok = r == W80211_OK;
+        if (!b.ok) std::fprintf(stderr, "ieee80211 decode: w80211_decode_submit / w80211_rx_collect: %s; batch dropped\n", w80211_last_error(d_ctx));
+        b.state = SET_READY;
     }
-    d_ncomplete = 0;
+    if (b.ok) {
+        const double t_p = d_trace ? trace_now() : 0.0;
+        const w80211_mpdu* m = b.out.mpdus;
+        for (uint32_t i = 0; i < b.out.n_mpdu; i++) publish(b.desc[m[i].pkt], b.bytes.data() + m[i].off, m[i].len, m[i].crc_ok != 0);
+        if (d_trace) d_t_publish += trace_now() - t_p;
+    }
+    d_queue.pop_front();
+    if (d_partial_in == idx) {
+        /* it still holds the LLRs of the packet being received (no other set was free): it carries on as the set being filled */
+        w80211_desc last = b.desc.back();
+        const uint64_t have = b.fill - (uint64_t)last.llr_off;
+        if (have) std::memmove(b.llr.data(), b.llr.data() + last.llr_off, (size_t)have * sizeof(float));
+        last.llr_off = 0;
+        b.desc.assign(1, last);
+        b.fill = have;
+        b.ncomplete = 0;
+        b.lease = 0;
+        b.state = SET_FILLING;
+        d_partial_in = -1;
+        d_cur = idx;
+    } else {
+        b.state = SET_FREE;
+    }
+    return true;
+}
+
+void decode_impl::drain_all()
+{
+    while (!d_queue.empty()) finish_front(true);
 }
 
 int decode_impl::general_work(int /*noutput_items*/,
@@ -242,27 +425,57 @@ int decode_impl::general_work(int /*noutput_items*/,
     const float* in = static_cast<const float*>(input_items[0]);
     const int navail = ninput_items[0];
     int consumed = 0;
-    while (consumed < navail && d_ncomplete < d_env.max_batch) {
-        if (d_left == 0) {
-            /* packet boundary: the reference idles until the first item carries tags (decode_impl.cc:68-70) */
-            if (!start_packet(nitems_read(0) + (uint64_t)consumed)) break;
+    bool published = false;
+    d_n_work++;
+    const double t_i = d_trace ? trace_now() : 0.0;
+    struct at_exit {
+        decode_impl* c;
+        double t;
+        ~at_exit()
+        {
+            if (c->d_trace) c->d_t_ingest += trace_now() - t; /* the whole call; submit / wait / publish are counted again inside */
         }
-        const long n = std::min<long>(navail - consumed, d_left);
-        const long ncopy = std::min(n, d_copy_left);
-        if (ncopy > 0) {
-            std::memcpy(d_llr.data() + d_fill, in + consumed, (size_t)ncopy * sizeof(float));
-            d_fill += (uint64_t)ncopy;
-            d_copy_left -= ncopy;
-            if (d_copy_left == 0) d_ncomplete++;
+    } guard{ this, t_i };
+    while (finish_front(false)) published = true;
+    take_free_set();
+    while (d_cur >= 0) {
+        bool stuck = false;
+        while (consumed < navail && d_cur >= 0 && d_sets[d_cur].ncomplete < d_env.max_batch) {
+            if (d_left == 0) {
+                /* packet boundary: the reference idles until the first item carries tags (decode_impl.cc:68-70) */
+                if (start_packet(nitems_read(0) + (uint64_t)consumed) != START_OK) {
+                    stuck = true;
+                    break;
+                }
+                if (d_cur < 0) break;
+            }
+            batch_set& b = d_sets[d_cur];
+            const long n = std::min<long>(navail - consumed, d_left);
+            const long ncopy = std::min(n, d_copy_left);
+            if (ncopy > 0) {
+                std::memcpy(b.llr.data() + b.fill, in + consumed, (size_t)ncopy * sizeof(float));
+                b.fill += (uint64_t)ncopy;
+                d_copy_left -= ncopy;
+                if (d_copy_left == 0) b.ncomplete++;
+            }
+            d_left -= n;
+            consumed += (int)n;
         }
-        d_left -= n;
-        consumed += (int)n;
+        if (d_cur < 0) break;
+        batch_set& b = d_sets[d_cur];
+        if (b.ncomplete == 0) break;
+        const bool drained = consumed == navail || stuck;
+        const double waited = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - b.oldest).count();
+        if (b.ncomplete >= d_env.max_batch || (drained && b.ncomplete >= d_env.min_batch) || waited >= d_env.max_wait_ms)
+            submit_current();
+        else
+            break;
+        if (drained) break;
     }
-    if (d_ncomplete > 0) {
-        const bool drained = consumed == navail;
-        const double waited = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - d_oldest).count();
-        if (d_ncomplete >= d_env.max_batch || (drained && d_ncomplete >= d_env.min_batch) || waited >= d_env.max_wait_ms)
-            run_batch();
+    if (consumed == 0 && !published && !d_queue.empty()) {
+        /* nothing else to do: wait for the oldest batch */
+        finish_front(true);
+        take_free_set();
     }
     consume_each(consumed);
     return 0;

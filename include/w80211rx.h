@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define W80211_ABI_VERSION 6
+#define W80211_ABI_VERSION 7
 
 /* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
 #define W80211_F_L 0
@@ -49,6 +49,7 @@ extern "C" {
 /* where the caller's sample / LLR / output buffers live */
 #define W80211_MEM_HOST 0   /* host memory (pinned or pageable); copies are part of the call */
 #define W80211_MEM_DEVICE 1 /* device memory of the ctx's GPU; nothing is copied */
+#define W80211_MEM_LEASE 2  /* w80211_decode_in only: the LLRs are a demod batch still in HBM, named by a lease handle */
 
 /* sample format of w80211_batch_in.iq[] (the IQ wire format of the host feed) */
 #define W80211_IQ_FC32 0 /* interleaved (re, im) binary32, what UHD hands to the reference's flowgraph */
@@ -258,7 +259,7 @@ typedef struct w80211_timing {
 
 int w80211_abi_version(void);
 /* sizeof of the ABI structs as compiled: 0 pkt_in, 1 batch_in, 2 desc, 3 mpdu, 4 batch_out, 5 stats, 6 timing, 7 cfg,
- * 8 sync, 9 signal_in, 10 signal_out, 11 detect_state, 12 detect_in, 13 detect_out
+ * 8 sync, 9 signal_in, 10 signal_out, 11 detect_state, 12 detect_in, 13 detect_out, 14 decode_in
  * (lets a binding written in another language check its own layout) */
 size_t w80211_sizeof(int what);
 int w80211_create(const w80211_cfg* cfg, w80211_ctx** out);
@@ -319,6 +320,38 @@ int w80211_decode_batch(w80211_ctx* ctx, int32_t npkt, const w80211_desc* desc, 
 int w80211_rx_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w80211_batch_out* out);
 int w80211_rx_collect(w80211_ctx* ctx, int slot);
 int w80211_rx_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_out* out);
+/* 1: w80211_rx_collect(ctx, slot) would not wait (the slot's batch has finished on the device), 0: still running, < 0: error.
+ * Also enqueues the second half of any batch whose header stage has finished, like every other call on the context. */
+int w80211_rx_poll(w80211_ctx* ctx, int slot);
+
+/* ---- the two blocks as separate, non-blocking stages (what gr/lib's demod / demod2 and decode call) ------------------
+ * The reference's demod and decode are two blocks joined by a float stream (demod_impl.cc:224-253 -> decode_impl.cc:60-121).
+ * demod_submit() is rx_submit() without the decode half: descriptors (and, with out->want_llr, the LLR stream) come back
+ * at w80211_rx_collect().  After that collect the batch's LLRs are still in HBM; w80211_llr_export() detaches them from the
+ * slot as a LEASE, a process-wide handle another context on the same GPU -- the decode block's -- can decode from without
+ * the 43 LLRs per payload byte crossing PCIe twice.  A producer keeps its W80211_LEASES_KEPT newest leases; exporting one
+ * more retires the oldest that no decode call is reading (its handle turns invalid, its memory is reused).
+ * decode_submit() is the non-blocking form of decode_batch(): LLRs from host memory (in->llr must stay valid until
+ * collect), device memory, or a lease (in->llr ignored; desc[p].llr_off are the offsets demod reported).  Results arrive
+ * at w80211_rx_collect(ctx, slot) in *out exactly as for decode_batch(). */
+#define W80211_LEASES_KEPT 6
+typedef struct w80211_decode_in {
+    int32_t npkt;
+    int32_t llr_mem;            /* W80211_MEM_HOST / W80211_MEM_DEVICE / W80211_MEM_LEASE: where llr (and, for DEVICE, desc) live */
+    const w80211_desc* desc;    /* [npkt]; always host memory for MEM_LEASE */
+    const float* llr;
+    uint64_t nllr;              /* floats in llr (ignored for MEM_LEASE) */
+    uint64_t lease;             /* MEM_LEASE: handle from w80211_llr_export() */
+} w80211_decode_in;
+int w80211_demod_submit(w80211_ctx* ctx, int slot, const w80211_batch_in* in, w80211_batch_out* out);
+int w80211_decode_submit(w80211_ctx* ctx, int slot, const w80211_decode_in* in, w80211_batch_out* out);
+/* slot must have been collected and not reused; *handle != 0 on success */
+int w80211_llr_export(w80211_ctx* ctx, int slot, uint64_t* handle);
+/* 0 and the lease's device / length when the handle is still valid, W80211_E_STATE when it has been retired */
+int w80211_llr_query(uint64_t handle, int32_t* device, uint64_t* nfloats);
+/* Consumers of leases in this process (each decode block adds 1 while it lives): a demod block in its default hand-off
+ * mode leaves the LLRs on the device only while this is > 0.  delta = 0 just reads the count. */
+int w80211_lease_consumers(int delta);
 
 /* ---- no-allocation decode (no counterpart in the reference) -----------
  * LLRs -> decoded trellis bits (what vstb_update + vstb_end leave in v_scramBits, lib/decode_impl.cc:205-302: still scrambled,

@@ -15,6 +15,7 @@
  * Test infrastructure only. */
 #pragma once
 #include <algorithm>
+#include <cstring>
 #include <gnuradio/block.h>
 
 namespace gr {
@@ -103,6 +104,110 @@ inline long mock_run(block& b,
         if (idle >= MOCK_IDLE_GROW && (!sees_all || win_out < 4096)) {
             if (!sees_all) win_in *= 2;
             if (win_out < 4096) win_out *= 2; /* largest atomic output: 1024 (NDP) / 832 LLRs */
+            idle = 0;
+            continue;
+        }
+        if (idle >= MOCK_IDLE_STOP) break;
+    }
+    return calls;
+}
+
+/* Two blocks joined by one bounded edge (demod -> decode), run in turn by one thread the way GNU Radio's single-threaded
+ * scheduler would: the upstream block writes straight into the edge's buffer (`ring_items` items; nothing is zero-filled
+ * or appended, so items a block produces without writing them cost nothing), the downstream block reads from it, and the
+ * buffer is compacted when its tail is reached.  Tags of the edge are dropped once consumed.  Returns the number of
+ * general_work calls; the downstream block's messages stay in its mock_msgs. */
+inline long mock_run_chain(block& up,
+                           block& down,
+                           const std::vector<const mock_stream*>& ins,
+                           long ring_items,
+                           long chunk_in,
+                           long chunk_out)
+{
+    const size_t nin = ins.size();
+    mock_stream mid(up.mock_outsig ? up.mock_outsig->sizeof_stream_item(0) : 4);
+    mid.tags_sorted = true;
+    if (ring_items < 4 * 4096) ring_items = 4 * 4096;
+    mid.data.resize((size_t)ring_items * mid.itemsize);
+    up.mock_in = ins;
+    up.mock_out.assign(1, &mid);
+    up.mock_nread.assign(nin, 0);
+    up.mock_nwritten.assign(1, 0);
+    up.mock_consumed.assign(nin, 0);
+    down.mock_in.assign(1, &mid);
+    down.mock_out.clear();
+    down.mock_nread.assign(1, 0);
+    down.mock_nwritten.clear();
+    down.mock_consumed.assign(1, 0);
+    std::vector<uint64_t> pos(nin, 0);
+    uint64_t w = 0, r = 0, base = 0; /* absolute item indices: written, read, and of mid.data[0] */
+    if (chunk_in <= 0) chunk_in = 1L << 40;
+    if (chunk_out <= 0) chunk_out = 8192;
+    long win_in = chunk_in;
+    int idle = 0;
+    long calls = 0;
+    for (;;) {
+        bool progress = false;
+        /* ---- upstream */
+        if ((long)(w - base) + chunk_out > ring_items && r > base) {
+            const uint64_t keep = w - r;
+            if (keep) std::memmove(mid.data.data(), mid.data.data() + (size_t)(r - base) * mid.itemsize, (size_t)keep * mid.itemsize);
+            base = r;
+        }
+        long room = std::min<long>(chunk_out, ring_items - (long)(w - base));
+        bool sees_all = true;
+        if (room > 0) {
+            gr_vector_int ninput(nin);
+            gr_vector_const_void_star in_ptrs(nin);
+            gr_vector_void_star out_ptrs(1);
+            for (size_t i = 0; i < nin; i++) {
+                uint64_t rem = ins[i]->nitems() - pos[i];
+                uint64_t n = std::min<uint64_t>(rem, (uint64_t)win_in);
+                if (n < rem) sees_all = false;
+                ninput[i] = (int)std::min<uint64_t>(n, 0x7fffffffu);
+                in_ptrs[i] = ins[i]->data.data() + pos[i] * ins[i]->itemsize;
+            }
+            out_ptrs[0] = mid.data.data() + (size_t)(w - base) * mid.itemsize;
+            std::fill(up.mock_consumed.begin(), up.mock_consumed.end(), 0);
+            const int produced = up.general_work((int)room, ninput, in_ptrs, out_ptrs);
+            calls++;
+            if (produced > 0) {
+                w += (uint64_t)produced;
+                up.mock_nwritten[0] = w;
+                progress = true;
+            }
+            for (size_t i = 0; i < nin; i++)
+                if (up.mock_consumed[i] > 0) {
+                    pos[i] += up.mock_consumed[i];
+                    up.mock_nread[i] += up.mock_consumed[i];
+                    progress = true;
+                }
+        }
+        /* ---- downstream */
+        {
+            gr_vector_int ninput(1, (int)std::min<uint64_t>(w - r, 0x7fffffffu));
+            gr_vector_const_void_star in_ptrs(1, mid.data.data() + (size_t)(r - base) * mid.itemsize);
+            gr_vector_void_star out_ptrs;
+            down.mock_consumed[0] = 0;
+            down.general_work(0, ninput, in_ptrs, out_ptrs);
+            calls++;
+            if (down.mock_consumed[0] > 0) {
+                r += (uint64_t)down.mock_consumed[0];
+                down.mock_nread[0] = r;
+                progress = true;
+                size_t k = 0;
+                while (k < mid.tags.size() && mid.tags[k].offset < r) k++;
+                if (k > 4096 || k == mid.tags.size()) mid.tags.erase(mid.tags.begin(), mid.tags.begin() + (long)k);
+            }
+        }
+        if (progress) {
+            idle = 0;
+            win_in = chunk_in;
+            continue;
+        }
+        idle++;
+        if (idle >= MOCK_IDLE_GROW && !sees_all) {
+            win_in *= 2;
             idle = 0;
             continue;
         }

@@ -4,6 +4,7 @@
  * Test infrastructure only; it also hosts this repo's own drop-in blocks in
  * the block-level equivalence tests. */
 #pragma once
+#include <algorithm>
 #include <chrono>
 #include <iostream>
 #include <cstdint>
@@ -22,8 +23,9 @@ struct mock_stream {
     int itemsize;
     std::vector<uint8_t> data;
     std::vector<tag_t> tags;
-    mock_stream() : itemsize(1) {}
-    explicit mock_stream(int isz) : itemsize(isz) {}
+    bool tags_sorted; /* tags are in ascending offset order: get_tags_in_range() may use a binary search */
+    mock_stream() : itemsize(1), tags_sorted(false) {}
+    explicit mock_stream(int isz) : itemsize(isz), tags_sorted(false) {}
     uint64_t nitems() const { return itemsize ? data.size() / itemsize : 0; }
 };
 
@@ -88,6 +90,11 @@ public:
     {
         v.clear();
         const mock_stream* s = mock_in.at(which_input);
+        if (s->tags_sorted) {
+            auto it = std::lower_bound(s->tags.begin(), s->tags.end(), abs_start, [](const tag_t& t, uint64_t o) { return t.offset < o; });
+            for (; it != s->tags.end() && it->offset < abs_end; ++it) v.push_back(*it);
+            return;
+        }
         for (const auto& t : s->tags)
             if (t.offset >= abs_start && t.offset < abs_end) v.push_back(t);
     }

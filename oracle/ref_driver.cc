@@ -12,6 +12,7 @@
  * THIS repo's drop-in blocks (gr/include, gr/lib) instead, into oracle/_ours/libours80211.so: the
  * block-level equivalence tests then feed identical streams to both libraries (tests/test_gr_blocks.py).
  */
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <string>
@@ -77,6 +78,12 @@ void ref_stream_add_tag_float(mock_stream* s, long offset, const char* key, floa
 void ref_stream_add_tag_c32(mock_stream* s, long offset, const char* key, const float* data, int n)
 {
     add_tag(s, offset, key, pmt::init_c32vector((size_t)n, reinterpret_cast<const std::complex<float>*>(data)));
+}
+/* tags were added in ascending offset order (or are put in that order now): lookups become binary searches */
+void ref_stream_sort_tags(mock_stream* s)
+{
+    std::stable_sort(s->tags.begin(), s->tags.end(), [](const gr::tag_t& a, const gr::tag_t& b) { return a.offset < b.offset; });
+    s->tags_sorted = true;
 }
 int ref_stream_ntags(const mock_stream* s) { return (int)s->tags.size(); }
 long ref_stream_tag_offset(const mock_stream* s, int i) { return (long)s->tags[i].offset; }
@@ -157,6 +164,22 @@ long ref_block_run(ref_block* b, mock_stream** ins, int nin, mock_stream** outs,
         b->msgs.push_back(payload->blob);
     }
     b->blk->mock_msgs.clear();
+    return calls;
+}
+/* demod -> decode joined by a bounded edge, run in turn by one thread (mock_run_chain): the streaming form both the
+ * block-path benchmark and the chain tests use.  Messages land in `down`. */
+long ref_chain_run(ref_block* up, ref_block* down, mock_stream** ins, int nin, long ring_items, long chunk_in, long chunk_out)
+{
+    std::vector<const mock_stream*> vin(ins, ins + nin);
+    long calls;
+    try {
+        calls = gr::mock_run_chain(*up->blk, *down->blk, vin, ring_items, chunk_in, chunk_out);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "ref_chain_run: exception: %s\n", e.what());
+        return -1;
+    }
+    for (auto& m : down->blk->mock_msgs) down->msgs.push_back(pmt::cdr(m.second)->blob);
+    down->blk->mock_msgs.clear();
     return calls;
 }
 int ref_block_nmsgs(const ref_block* b) { return (int)b->msgs.size(); }

@@ -46,6 +46,9 @@ def lib():
         L.ref_stream_add_tag_long.argtypes = [vp, cl, C.c_char_p, cl]
         L.ref_stream_add_tag_float.argtypes = [vp, cl, C.c_char_p, cf]
         L.ref_stream_add_tag_c32.argtypes = [vp, cl, C.c_char_p, vp, ci]
+        L.ref_stream_sort_tags.argtypes = [vp]
+        L.ref_chain_run.restype = cl
+        L.ref_chain_run.argtypes = [vp, vp, C.POINTER(vp), ci, cl, cl, cl]
         L.ref_stream_ntags.argtypes = [vp]
         L.ref_stream_tag_offset.restype = cl
         L.ref_stream_tag_offset.argtypes = [vp, ci]
@@ -247,6 +250,31 @@ def run_decode(llr_stream, debug=False, chunk_in=0, chunk_out=8192):
     return blk.messages()
 
 
+def run_chain(sig_streams, mupos=0, mugid=2, debug=False, ring_items=1 << 20, chunk_in=0, chunk_out=8192, blocks=None, timing=None):
+    """demod / demod2 -> decode joined by a bounded edge and run in turn by one thread (mock_run_chain), the way a
+    flowgraph streams: signal-format stream(s) -> list of published blobs.  blocks: an (upstream, downstream) pair to
+    reuse (both must stand at a packet boundary); timing: a dict that receives the seconds spent inside the two blocks'
+    run ("chain_s") and the general_work calls made."""
+    import time
+    L = lib()
+    if blocks is None:
+        blocks = chain_blocks(len(sig_streams), mupos, mugid, debug)
+    up, down = blocks
+    arr = (C.c_void_p * len(sig_streams))(*[s.h for s in sig_streams])
+    t0 = time.perf_counter()
+    r = L.ref_chain_run(up.h, down.h, arr, len(sig_streams), ring_items, chunk_in, chunk_out)
+    if timing is not None:
+        timing["chain_s"] = time.perf_counter() - t0
+        timing["calls"] = int(r)
+    if r < 0:
+        raise RuntimeError("block raised")
+    return down.messages()
+
+
+def chain_blocks(nant=1, mupos=0, mugid=2, debug=False):
+    return (Block("demod", mupos, mugid) if nant == 1 else Block("demod2")), Block("decode", 1 if debug else 0)
+
+
 def make_sig_stream(packets, nant=1):
     """Build demod-input stream(s) from packet dicts:
     {'iq': [ant0, ant1?] complex64 arrays of nsamp samples, 'l_mcs', 'l_len', 'chan': c64[64],
@@ -273,6 +301,7 @@ def make_sig_stream(packets, nant=1):
         s.add_tag(off, "len", int(p["l_len"]))
         s.add_tag(off, "nsamp", int(nsamp))
         s.add_tag(off, "chan", np.asarray(p["chan"], np.complex64))
+    lib().ref_stream_sort_tags(streams[0].h)
     return streams
 
 

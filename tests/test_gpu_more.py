@@ -341,6 +341,65 @@ def test_submit_collect_errors_leave_the_slot_usable():
         rx2.close()
 
 
+def test_demod_and_decode_as_separate_non_blocking_stages_joined_by_llr_leases():
+    """What the two GR blocks do (ABI 7): w80211_demod_submit on one context, the batch's LLRs exported as a lease after
+    collect, w80211_decode_submit on ANOTHER context of the same GPU reading that lease -- two batches in flight on each
+    side.  Results equal the fused path's; a producer keeps its W80211_LEASES_KEPT newest leases, older handles turn
+    invalid and decode refuses them; destroying the producer retires the rest."""
+    dm, dc = host.Receiver(0, nslots=2), host.Receiver(0, nslots=2)
+    try:
+        batches = [gp.gen_batch(g.F_L, 7, 1, 700, 5, snr_db=30, seed=170), gp.gen_batch(g.F_HT, 7, 1, 1200, 4, snr_db=30, short_gi=True, seed=171),
+                   gp.gen_batch(g.F_VHT, 8, 1, 2000, 3, snr_db=30, seed=172), gp.gen_batch(g.F_HT, 12, 2, 900, 3, snr_db=35, seed=173)]
+        packed = [host.pack_batch([b]) for b in batches]
+        fused = [dc.rx(*p) for p in packed]
+        leases, descs = [], []
+        for i0 in (0, 2):
+            for k in (0, 1):
+                dm.demod_submit(k, *packed[i0 + k], want_llr=False)
+            for k in (0, 1):
+                while not dm.poll(k):
+                    pass
+                r = dm.collect(k)
+                descs.append(r.desc.copy())
+                leases.append(dm.llr_export(k))
+        assert len(set(leases)) == 4 and all(dm.llr_query(h)[0] == 0 for h in leases)
+        for i0 in (0, 2):
+            for k in (0, 1):
+                dc.decode_submit(k, descs[i0 + k], lease=leases[i0 + k])
+            for k in (0, 1):
+                r = dc.collect(k)
+                r.desc = descs[i0 + k]
+                assert r.messages() == fused[i0 + k].messages() and len(r.messages()) == len(batches[i0 + k]["mpdu"])
+        # host LLRs through the same non-blocking call, decoded from where they are staged (aligned offsets)
+        full = dm.demod(*packed[2])
+        dc.decode_submit(0, full.desc, llr=full.llr[: full.n_llr])
+        r = dc.collect(0)
+        r.desc = full.desc
+        assert r.messages() == fused[2].messages()
+        # more exports than the producer keeps: the oldest handles retire
+        for n in range(4):
+            dm.demod_submit(0, *packed[0], want_llr=False)
+            dm.collect(0)
+            leases.append(dm.llr_export(0))
+        assert dm.llr_query(leases[0]) is None and dm.llr_query(leases[1]) is None and dm.llr_query(leases[-1]) is not None
+        with pytest.raises(host.W80211Error):
+            dc.decode_submit(0, descs[0], lease=leases[0])
+        dc.decode_submit(0, descs[0], lease=leases[-1])  # the slot is usable after the refusal; same packets as batch 0
+        r = dc.collect(0)
+        r.desc = descs[0]
+        assert r.messages() == fused[0].messages()
+        # a reader in flight keeps a lease's memory alive while its producer is destroyed
+        dc.decode_submit(1, descs[0], lease=leases[-1])
+        dm.close()
+        r = dc.collect(1)
+        r.desc = descs[0]
+        assert r.messages() == fused[0].messages()
+        assert dc.llr_query(leases[-1]) is None
+    finally:
+        dm.close()
+        dc.close()
+
+
 @pytest.mark.parametrize("fmt,mcs,length,sgi", [(0, 7, 1500, False), (1, 7, 4095, True), (2, 8, 4088, False), (2, 3, 77, True)])
 def test_llrs_equal_the_plain_c_port(rx, fmt, mcs, length, sgi):
     """The CUDA demod against the plain-C restatement of the reference's per-symbol demodulation (oracle/port/demod_port.c),

@@ -24,6 +24,13 @@ def ours(refgr):
     return refgr.load_harness(OURS_PATH)
 
 
+@pytest.fixture(autouse=True)
+def host_llr_items(monkeypatch):
+    """The block-by-block tests compare demod's output items with the reference's, so the LLRs must be in them: the
+    hand-off tests below choose their own mode (gr/lib/demod_core.h)."""
+    monkeypatch.setenv("W80211_LLR_HANDOFF", "host")
+
+
 def packets_of(batches):
     pk = []
     for b in batches:
@@ -100,6 +107,59 @@ def test_small_batches_from_the_environment(refgr, ours, monkeypatch):
     our_llr = ours.run_demod(ours.make_sig_stream(pk))
     same_llr_stream(our_llr, ref_llr)
     assert ours.run_decode(our_llr) == refgr.run_decode(ref_llr)
+
+
+def test_chain_runner_equals_block_by_block_on_the_reference(refgr):
+    """oracle/mock_scheduler.h mock_run_chain (demod -> decode over a bounded edge, one thread) publishes what the two
+    reference blocks publish when each runs over whole streams -- for any edge size and chunking (CPU only)."""
+    pk = packets_of([gp.gen_batch(g.F_L, 4, 1, 120, 3, snr_db=30, seed=31), gp.gen_batch(g.F_VHT, 5, 1, 260, 3, snr_db=30, seed=32),
+                     gp.gen_batch(g.F_HT, 1, 1, 90, 2, snr_db=30, seed=33, corrupt_fcs=True)])
+    want = refgr.run_decode(refgr.run_demod(refgr.make_sig_stream(pk)))
+    assert len(want) == 6
+    for ring, cin, cout in [(1 << 20, 0, 8192), (16384, 1500, 1024), (16384, 333, 4096)]:
+        assert refgr.run_chain(refgr.make_sig_stream(pk), ring_items=ring, chunk_in=cin, chunk_out=cout) == want
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["auto", "device", "both", "host"])
+@pytest.mark.parametrize("batch", [(2048, 1), (3, 3), (2, 1)])
+@pytest.mark.parametrize("nant", [1, 2])
+def test_streaming_chain_in_every_handoff_mode(refgr, ours, monkeypatch, mode, batch, nant):
+    """demod -> decode streamed over a bounded edge: batches in flight in both blocks, LLRs handed over in HBM (device: the
+    stream items are not even written), on the host, or both; small batches force many leases, several sets per block and
+    packets cut by a batch boundary.  The published messages are the reference chain's."""
+    monkeypatch.setenv("W80211_LLR_HANDOFF", mode)
+    monkeypatch.setenv("W80211_MAX_BATCH", str(batch[0]))
+    monkeypatch.setenv("W80211_MIN_BATCH", str(batch[1]))
+    pk = packets_of(mixed_batches(nant))
+    want = refgr.run_decode(refgr.run_demod(refgr.make_sig_stream(pk, nant=nant)))
+    assert len(want) >= 12
+    for ring, cin, cout in [(1 << 20, 0, 8192), (20000, 3000, 2048)]:
+        got = ours.run_chain(ours.make_sig_stream(pk, nant=nant), ring_items=ring, chunk_in=cin, chunk_out=cout)
+        assert got == want, (ring, len(got), len(want))
+
+
+@pytest.mark.gpu
+def test_device_handoff_writes_no_llr_items(refgr, ours, monkeypatch):
+    """W80211_LLR_HANDOFF=device: demod's stream has the reference's tags plus the lease tags, `total` items per packet,
+    and the items are left unwritten; `both` carries the reference's LLRs as well.  A decode block that finds the lease
+    retired falls back to the items when they exist and drops the packet (and says so) when they do not."""
+    pk = packets_of(mixed_batches(1, n=2))
+    ref_llr = refgr.run_demod(refgr.make_sig_stream(pk))
+    monkeypatch.setenv("W80211_LLR_HANDOFF", "both")
+    both = ours.run_demod(ours.make_sig_stream(pk))
+    assert np.array_equal(both.data(), ref_llr.data())
+    monkeypatch.setenv("W80211_LLR_HANDOFF", "device")
+    dev = ours.run_demod(ours.make_sig_stream(pk))
+    assert dev.data().shape == ref_llr.data().shape and not dev.data().any()
+    for s in (both, dev):
+        for (o, x), (o2, y) in zip(s.tags(), ref_llr.tags()):
+            assert o == o2 and set(x) - set(y) <= {"w80211_llr", "w80211_off", "w80211_nohost"} and set(y) <= set(x)
+            assert x["w80211_llr"] > 0 and x["w80211_off"] % 4 == 0 and ("w80211_nohost" in x) == (s is dev)
+    # the demod blocks are gone and with them their leases: `both` still decodes from the items, `device` cannot
+    want = refgr.run_decode(ref_llr)
+    assert ours.run_decode(both) == want
+    assert ours.run_decode(dev) == []
 
 
 def _capture_stdout(fn):

@@ -104,16 +104,16 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(host.SYMBOLS), declared ^ set(host.SYMBOLS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.w80211_abi_version() == 6
+    assert L.w80211_abi_version() == 7
 
 
 def test_struct_layouts_match():
     L = host.load()
-    sizes = [L.w80211_sizeof(i) for i in range(14)]
+    sizes = [L.w80211_sizeof(i) for i in range(15)]
     mine = [C.sizeof(host.PktIn), C.sizeof(host.BatchIn), host.DESC_DTYPE.itemsize, host.MPDU_DTYPE.itemsize,
             C.sizeof(host.BatchOut), C.sizeof(host.Stats), C.sizeof(host.Timing), C.sizeof(host.Cfg),
             host.SYNC_DTYPE.itemsize, C.sizeof(host.SignalIn), C.sizeof(host.SignalOut),
-            C.sizeof(host.DetectState), C.sizeof(host.DetectIn), C.sizeof(host.DetectOut)]
+            C.sizeof(host.DetectState), C.sizeof(host.DetectIn), C.sizeof(host.DetectOut), C.sizeof(host.DecodeIn)]
     assert sizes == mine
     assert host.PKT_IN_DTYPE.itemsize == sizes[0]
 
