@@ -33,10 +33,19 @@
 #include <unordered_map>
 #include <vector>
 #include "common.cuh"
+#include <nvtx3/nvToolsExt.h> /* header-only; ranges show up in Nsight Systems timelines, cost nothing without a tool attached */
 
 extern "C" void w80211_fill_tables(W80211Tables* t);
 
 namespace {
+
+/* one NVTX range per host-side stage of a batch (tracing) */
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 struct DevBuf {
     void* p = nullptr;
@@ -260,6 +269,7 @@ inline long long llr_needed(int trellis, int cr)
 /* Host plan after the header stage.  Fills llr offsets in h_desc, uploads the plan arrays. */
 int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, bool do_decode)
 {
+    NvtxRange nvtx_("w80211 host plan + upload");
     const int npkt = s.npkt;
     /* One pass over the descriptors (12 MB for a full batch; the later loops only touch a 4-byte key per packet): LLR
      * layout, symbol prefix sums, and the packets to decode with their sort key (code rate ascending, trellis descending). */
@@ -395,6 +405,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
 
 int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
 {
+    NvtxRange nvtx_("w80211 enqueue viterbi/traceback/post");
     cudaStream_t st = s.stream;
     w80211_batch_out* out = s.out;
     CK(cudaEventRecord(s.ev[EV_VIT0], st));
@@ -478,6 +489,7 @@ int finish_outputs(w80211_ctx* ctx, Slot& s)
  * back to the host.  Does not wait. */
 int enqueue_input_header(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w80211_batch_out* out, bool do_decode)
 {
+    NvtxRange nvtx_("w80211 enqueue input copies + header");
     if (!in || !out || in->npkt < 0 || (in->nant != 1 && in->nant != 2) || !in->iq[0] || (in->nant == 2 && !in->iq[1]) ||
         (in->npkt > 0 && (!in->pkts || !in->chan)) || (in->iq_format != W80211_IQ_FC32 && in->iq_format != W80211_IQ_SC16 && in->iq_format != W80211_IQ_SC8))
         return fail(ctx, W80211_E_ARG, "bad batch_in");
@@ -574,6 +586,7 @@ int enqueue_input_header(w80211_ctx* ctx, Slot& s, const w80211_batch_in* in, w8
 /* second half of the front: the descriptors are on the host (EV_HDRD has completed); plan, then demod */
 int continue_front(w80211_ctx* ctx, Slot& s)
 {
+    NvtxRange nvtx_("w80211 enqueue demod");
     cudaStream_t st = s.stream;
     const int npkt = s.npkt;
     const bool do_decode = s.did_decode;
@@ -625,6 +638,7 @@ int launch_post_again(w80211_ctx* ctx, Slot& s, uint32_t need)
 
 int collect_slot(w80211_ctx* ctx, Slot& s)
 {
+    NvtxRange nvtx_("w80211 collect");
     if (!s.busy) return fail(ctx, W80211_E_STATE, "slot idle: nothing to collect");
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(s.stream));
@@ -1075,6 +1089,7 @@ int w80211_lease_consumers(int delta)
 
 int w80211_presiso_batch(w80211_ctx* ctx, const float* sig, uint64_t nsamples, int32_t mem, float* preac, float* preconj)
 {
+    NvtxRange nvtx_("w80211 presiso_batch");
     if (!ctx) return W80211_E_ARG;
     if (nsamples > 0 && (!sig || !preac || !preconj)) return fail(ctx, W80211_E_ARG, "bad presiso_batch arguments");
     if (nsamples == 0) return W80211_OK;
@@ -1105,6 +1120,7 @@ int w80211_presiso_batch(w80211_ctx* ctx, const float* sig, uint64_t nsamples, i
 
 int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_detect_out* out)
 {
+    NvtxRange nvtx_("w80211 detect_batch");
     if (!ctx) return W80211_E_ARG;
     if (!in || !out || in->nsamples >= 0xffffffffull || (in->nsamples > 0 && (!in->preac || !in->preconj || !in->sig)) ||
         out->sync_capacity < 0 || (out->sync_capacity > 0 && !out->syncs))
@@ -1297,6 +1313,7 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
 
 int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_signal_out* out)
 {
+    NvtxRange nvtx_("w80211 signal_batch");
     if (!ctx) return W80211_E_ARG;
     if (!in || !out || in->nsync < 0 || (in->nant != 1 && in->nant != 2) || (in->nsync > 0 && !in->syncs) ||
         (in->nsamples > 0 && (!in->iq[0] || (in->nant == 2 && !in->iq[1]))) || in->start > in->nsamples)
@@ -1464,6 +1481,7 @@ int w80211_demod_batch(w80211_ctx* ctx, const w80211_batch_in* in, w80211_batch_
 /* LLRs + descriptors -> everything of the decode half enqueued on the slot's stream; does not wait */
 static int decode_submit_impl(w80211_ctx* ctx, int slot, const w80211_decode_in* in, w80211_batch_out* out)
 {
+    NvtxRange nvtx_("w80211 decode_submit");
     if (slot < 0 || slot >= ctx->nslots) return fail(ctx, W80211_E_ARG, "bad slot %d", slot);
     if (!in || !out || in->npkt < 0 || (in->npkt > 0 && !in->desc) || in->llr_mem < W80211_MEM_HOST || in->llr_mem > W80211_MEM_LEASE ||
         (in->npkt > 0 && in->llr_mem != W80211_MEM_LEASE && !in->llr))

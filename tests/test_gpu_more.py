@@ -341,6 +341,43 @@ def test_submit_collect_errors_leave_the_slot_usable():
         rx2.close()
 
 
+def test_llrs_outside_the_stated_domain_never_publish_a_wrong_frame(refgr, rx):
+    """DESIGN.md 3 states the Viterbi's input domain: finite LLRs whose path sums stay above the reference's -1e15 sentinel.
+    Outside it (NaN / Inf from a zero channel bin, values that overflow binary32) the two decoders need not agree bit for
+    bit -- the reference never selects a NaN candidate and keeps the sentinel, fmaxf drops the NaN -- so which of those
+    packets still decode may differ; but neither side hangs or faults, neither publishes a frame that was not sent (the
+    FCS guards both), hugely scaled but finite LLRs decode like the reference's, and clean packets of the same batch are
+    untouched."""
+    bs = [gp.gen_batch(g.F_HT, 5, 1, 600, 7, snr_db=30, seed=640)]
+    ref_pkts, ref_msgs = ref_chain(refgr, bs)
+    assert len(ref_msgs) == 7
+    pk = [dict(p) for p in ref_pkts]
+    rng = np.random.default_rng(3)
+    pk[1]["llr"] = pk[1]["llr"].copy(); pk[1]["llr"][100::52] = np.nan          # one dead subcarrier
+    pk[2]["llr"] = pk[2]["llr"].copy(); pk[2]["llr"][rng.integers(0, 5000, 40)] = np.inf
+    pk[3]["llr"] = pk[3]["llr"].copy() * np.float32(1e30)                        # finite, far below the sentinel on bad paths
+    pk[4]["llr"] = np.full_like(pk[4]["llr"], np.nan)
+    pk[5]["llr"] = pk[5]["llr"].copy() * np.float32(3e37)                        # sums overflow to +-Inf, Inf - Inf = NaN
+    want = refgr.run_decode(refgr.make_llr_stream(pk))
+    desc = np.zeros(len(pk), host.DESC_DTYPE)
+    off = 0
+    for i, r in enumerate(pk):
+        for k in ("format", "mcs", "len", "cr", "ampdu", "trellis", "total"):
+            desc[k][i] = r[k]
+        desc["llr_off"][i] = off
+        off += (r["total"] + 3) & ~3
+    llr = np.zeros(off + 8, np.float32)
+    for i, r in enumerate(pk):
+        llr[desc["llr_off"][i]: desc["llr_off"][i] + r["total"]] = r["llr"]
+    got = rx.decode(desc, llr).messages()
+    for side in (got, want):
+        assert all(m in ref_msgs for m in side) and len(set(side)) == len(side)
+        assert ref_msgs[0] in side and ref_msgs[6] in side and ref_msgs[3] in side
+        assert ref_msgs[4] not in side
+    in_domain = lambda ms: [m for m in ms if m in (ref_msgs[0], ref_msgs[3], ref_msgs[6])]
+    assert in_domain(got) == in_domain(want)
+
+
 def test_demod_and_decode_as_separate_non_blocking_stages_joined_by_llr_leases():
     """What the two GR blocks do (ABI 7): w80211_demod_submit on one context, the batch's LLRs exported as a lease after
     collect, w80211_decode_submit on ANOTHER context of the same GPU reading that lease -- two batches in flight on each
@@ -416,3 +453,22 @@ def test_llrs_equal_the_plain_c_port(rx, fmt, mcs, length, sgi):
         assert int(d["status"]) == host.ST_OK and int(d["format"]) == fmt
         want = port.demod_packet(b["post"][0][p], b["chan"][p], fmt, int(d["nbpscs"]), int(d["nsym"]), short_gi=sgi)
         assert np.array_equal(res.packet_llr(p), want)
+
+
+def test_one_context_per_device_in_one_process():
+    """one ctx per GPU.  Two contexts in one process, on devices 0 and 1 (needs two GPUs: run under
+    `gpurun --gpus 2`), each sets its own per-device kernel attributes and decodes its own batch; batches interleaved."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    a, b = host.Receiver(0), host.Receiver(1)
+    try:
+        bs = [gp.gen_batch(g.F_HT, 15, 2, 1500, 6, snr_db=35, seed=910), gp.gen_batch(g.F_VHT, 8, 1, 3000, 6, snr_db=30, seed=911)]
+        packed = [host.pack_batch([x]) for x in bs]
+        a.submit(0, *packed[0]); b.submit(0, *packed[1]); a.submit(1, *packed[1]); b.submit(1, *packed[0])
+        ra0, rb0, ra1, rb1 = a.collect(0), b.collect(0), a.collect(1), b.collect(1)
+        for r, x in ((ra0, bs[0]), (rb1, bs[0]), (rb0, bs[1]), (ra1, bs[1])):
+            assert [m[3:-1] for m in r.messages()] == [y.tobytes() for y in x["mpdu"]]
+    finally:
+        a.close()
+        b.close()

@@ -31,12 +31,13 @@ def llr_close(a, b, scale):
     return np.all(np.abs(a - b) <= 1e-4 * np.maximum(np.maximum(np.abs(a), np.abs(b)), scale))
 
 
-def compare_with_reference(refgr, rx, batches, exact_llr=True):
+def compare_with_reference(refgr, rx, batches, exact_llr=True, ref=None):
     """Run both sides on the same samples and assert tags, LLRs and published messages agree.
+    ref: the reference side's (packets, messages) when the caller has run it already.
     Returns (our Result, reference messages)."""
     iq, pkts, chan = host.pack_batch(batches)
     res = rx.rx(iq, pkts, chan, want_llr=True)
-    ref_pkts, ref_msgs = ref_chain(refgr, batches)
+    ref_pkts, ref_msgs = ref if ref is not None else ref_chain(refgr, batches)
     ok_idx = [p for p in range(len(pkts)) if res.desc[p]["status"] == host.ST_OK]
     assert len(ok_idx) == len(ref_pkts), "packets that reach the demod loop: %d vs reference %d" % (len(ok_idx), len(ref_pkts))
     for p, r in zip(ok_idx, ref_pkts):
