@@ -11,4 +11,4 @@ for f in hdr demod viterbi post iqconv detect capi; do
 done
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Xcompiler -fPIC -x cu -c tables.cc -o /tmp/w80211_$name/tables.o &
 wait
-/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libw80211rx_$name.so /tmp/w80211_$name/*.o -lcudart
+/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libw80211rx_$name.so /tmp/w80211_$name/*.o -lcudart -ldl

@@ -40,6 +40,10 @@ struct W80211Tables {
      * 0..3 legacy nbpscs 1,2,4,6; 4..8 HT/VHT one stream nbpscs 1,2,4,6,8;
      * 9..13 two streams, stream 1 (deinterleave + stream de-parse); 14..18 stream 2. */
     uint16_t map[W_NMAPS][W_MAPLEN];
+    /* map[] again, indexed [FFT bin][bit], 16 bytes per bin: binmap[m][i][b] = map[m][j(i) * nb + b], or the symbol's LLR count
+     * (the staging row's dump slot) for bins without data and bits the modulation does not have */
+    uint16_t binmap_align_[4]; /* keeps binmap on a 16-byte boundary (checked in demod.cu) */
+    uint16_t binmap[W_NMAPS][64][8];
     /* CRC-32 (reflected 0xEDB88320) for post.cu: slice-by-4 tables (crc_tab[0] is the byte table) and x^(2^k) mod P */
     uint32_t crc_tab[4][256];
     uint32_t crc_x2n[32];

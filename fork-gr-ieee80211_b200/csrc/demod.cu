@@ -10,8 +10,10 @@
  * The running state of the reference (pilot polarity index, pilot rotation) is a closed form of the
  * symbol number here, so symbols are independent.  A work item is a run of up to W_DEMOD_SPC symbols of one packet, walked by one
  * 8-lane group with the next symbol's samples prefetched; reads: nRx * 64 complex samples per
- * symbol (coalesced 64-byte segments); the symbol's nCBPS LLRs are scattered (deinterleaved) into
- * shared memory and leave as coalesced 16-byte vectors.
+ * symbol (coalesced 64-byte segments); the symbol's nCBPS LLRs are scattered (deinterleaved) into a
+ * staging row in shared memory, which one lane of the group hands to the copy engine of the SM as a single
+ * bulk store (cp.async.bulk shared -> global, 192 .. 3328 bytes): no lane spends load / store slots on the
+ * copy-out, and the next symbol's FFT and equalisation run while the row drains.
  */
 #include "common.cuh"
 
@@ -22,24 +24,10 @@
 #define DEMOD_GROUPS (DEMOD_THREADS / 8)
 #define DEMOD_SPC W_DEMOD_SPC /* most symbols per work item (one 8-lane group walks them in order) */
 #define DEMOD_STAGE 832    /* floats: largest nCBPS (2 streams of 256-QAM) */
-#ifndef DEMOD_PAD
 #define DEMOD_PAD 4        /* floats after a group's staging row: rows start 4 banks apart (the deinterleaved positions of the
                               8 bins a group writes at a time fall on 8 banks that repeat every row of 416 / 832 floats) and
                               stay 16-byte aligned for the copy-out; the pad is the slot that bins without data write to */
-#endif
 #define DEMOD_MAPPAD 8     /* map entries after a table, all pointing at that slot */
-#ifndef DEMOD_NOHOIST
-#define DEMOD_NOHOIST 1
-#endif
-#ifndef DEMOD_HOIST
-#define DEMOD_HOIST 2
-#endif
-#ifndef DEMOD_EQHOIST
-#define DEMOD_EQHOIST 0
-#endif
-#ifndef DEMOD_BRANCHFREE
-#define DEMOD_BRANCHFREE 1
-#endif
 
 /* item -> packet: prefix[p] <= w < prefix[p+1].  Batches are mostly homogeneous, so an
  * interpolated guess is tried before the binary search. */
@@ -58,73 +46,80 @@ __device__ __forceinline__ int find_packet(const int* __restrict__ prefix, int n
     return lo;
 }
 
-/* max-log LLRs of one axis value (already scaled), written through the deinterleave table (procSymQamToLlr,
- * cloud80211phy.cc:2090-2148); HALF = bits per axis, a compile-time constant so the chain has no branches */
-template <int HALF>
-__device__ __forceinline__ void axis_llr(float v, const uint16_t* __restrict__ map, float* __restrict__ out)
+/* One bin's row of the scatter table (W80211Tables::binmap): eight 16-bit indices into the group's staging row, bit b of the
+ * bin's subcarrier goes to out[idx<b>]; one 16-byte load per bin and lane, straight from global memory (19 KB for all
+ * modulations, shared by every block: L1 hits). */
+template <int E>
+__device__ __forceinline__ uint32_t map_idx(const uint4& m)
 {
-    out[map[0]] = v;
+    const uint32_t w = E < 2 ? m.x : (E < 4 ? m.y : (E < 6 ? m.z : m.w));
+    return (E & 1) ? (w >> 16) : (w & 0xffffu);
+}
+
+/* max-log LLRs of one axis value (already scaled), written through the scatter table (procSymQamToLlr,
+ * cloud80211phy.cc:2090-2148); HALF = bits per axis, E0 = the axis' first table entry: compile-time, so the chain has no
+ * branches */
+template <int HALF, int E0>
+__device__ __forceinline__ void axis_llr(float v, const uint4& m, float* __restrict__ out)
+{
+    out[map_idx<E0>(m)] = v;
     if (HALF >= 2) {
         float thr = HALF == 2 ? 2.0f : (HALF == 3 ? 4.0f : 8.0f);
         float l = __fsub_rn(thr, fabsf(v));
-        out[map[1]] = l;
+        out[map_idx<E0 + 1>(m)] = l;
         if (HALF >= 3) {
             thr = __fmul_rn(thr, 0.5f);
             l = __fsub_rn(thr, fabsf(l));
-            out[map[2]] = l;
+            out[map_idx<E0 + 2>(m)] = l;
             if (HALF >= 4) {
                 l = __fsub_rn(2.0f, fabsf(l));
-                out[map[3]] = l;
+                out[map_idx<E0 + 3>(m)] = l;
             }
         }
     }
 }
 
 template <int NB>
-__device__ __forceinline__ void qam_llr(cf32 q, const uint16_t* __restrict__ map /* + j * NB */, float* __restrict__ out)
+__device__ __forceinline__ void qam_llr(cf32 q, const uint4& m, float* __restrict__ out)
 {
     if (NB == 1) {
-        out[map[0]] = q.x;
+        out[map_idx<0>(m)] = q.x;
         return;
     }
     /* reference constants, cloud80211phy.cc:2105,2114,2125,2138 */
     const float sc = NB == 2 ? 1.4142135623730951f : (NB == 4 ? 3.1622776601683795f : (NB == 6 ? 6.48074069840786f : 13.038404810405298f));
     q = c_scale(q, sc);
-    axis_llr<(NB >> 1)>(q.x, map, out);
-    axis_llr<(NB >> 1)>(q.y, map + (NB >> 1), out);
+    axis_llr<(NB >> 1), 0>(q.x, m, out);
+    axis_llr<(NB >> 1), (NB >> 1)>(q.y, m, out);
 }
 
 /* The LLRs of one symbol: q = eq * conj(pilot sum) / |pilot sum| per data subcarrier, demapped and scattered into the
- * group's staging block in coded-bit order.  No branch per bin: a bin without data takes the table's pad entries and
- * lands in the row's pad slot.  q = a / pa goes through y = RN(1/pa) (f_div_known); unsafe divisors and tiny quotients
+ * group's staging block in coded-bit order.  No branch per bin: the table rows of a bin without data point at the dump slot
+ * after the symbol's LLRs.  q = a / pa goes through y = RN(1/pa) (f_div_known); unsafe divisors and tiny quotients
  * (where the FMA residual could leave the normal range) are found per symbol, not per bin, and the whole symbol is then
  * redone with the plain division. */
 template <int NB, bool MIMO, bool SLOW>
 __device__ __forceinline__ bool symbol_llrs_pass(const cf32 (&e1)[8], const cf32 (&e2)[8], const int (&jj)[8], bool two, cf32 ps, float pa,
-                                                 float rpa, const uint16_t* __restrict__ map1, const uint16_t* __restrict__ map2,
+                                                 float rpa, const uint4* __restrict__ map1, const uint4* __restrict__ map2,
                                                  float* __restrict__ stg)
 {
     bool bad = false;
 #pragma unroll
     for (int k2 = 0; k2 < 8; k2++) {
         const int j = jj[k2];
-#if DEMOD_BRANCHFREE
-        const int mo = j >= 0 ? j * NB : W_MAPLEN;
-#else
-        const int mo = j * NB;
-        if (j < 0) continue;
-#endif
         {
+            const uint4 m = __ldg(map1 + 8 * k2);
             const cf32 a = c_mul(e1[k2], ps);
             const cf32 q = SLOW ? c_divf(a, pa) : c_make(f_div_known(a.x, pa, rpa), f_div_known(a.y, pa, rpa));
             if (!SLOW) bad = bad || (j >= 0 && !(fabsf(q.x) >= 1e-30f && fabsf(q.y) >= 1e-30f));
-            qam_llr<NB>(q, map1 + mo, stg);
+            qam_llr<NB>(q, m, stg);
         }
         if (MIMO && two) {
+            const uint4 m = __ldg(map2 + 8 * k2);
             const cf32 a = c_mul(e2[k2], ps);
             const cf32 q = SLOW ? c_divf(a, pa) : c_make(f_div_known(a.x, pa, rpa), f_div_known(a.y, pa, rpa));
             if (!SLOW) bad = bad || (j >= 0 && !(fabsf(q.x) >= 1e-30f && fabsf(q.y) >= 1e-30f));
-            qam_llr<NB>(q, map2 + mo, stg);
+            qam_llr<NB>(q, m, stg);
         }
     }
     return bad;
@@ -132,22 +127,13 @@ __device__ __forceinline__ bool symbol_llrs_pass(const cf32 (&e1)[8], const cf32
 
 template <int NB, bool MIMO>
 __device__ __forceinline__ void symbol_llrs(const cf32 (&e1)[8], const cf32 (&e2)[8], const int (&jj)[8], bool two, cf32 ps, float pa,
-                                            const uint16_t* __restrict__ map1, const uint16_t* __restrict__ map2, float* __restrict__ stg)
+                                            const uint4* __restrict__ map1, const uint4* __restrict__ map2, float* __restrict__ stg)
 {
     const bool slow_pa = f_recip_unsafe(pa) || !(pa > 1e-30f) || !(pa < 1e30f);
     const float rpa = __frcp_rn(pa);
-#if DEMOD_HOIST == 2
     bool redo = slow_pa;
     if (!slow_pa) redo = symbol_llrs_pass<NB, MIMO, false>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
     if (redo) symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
-#elif DEMOD_HOIST == 1
-    if (slow_pa)
-        symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
-    else if (symbol_llrs_pass<NB, MIMO, false>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg))
-        symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
-#else
-    symbol_llrs_pass<NB, MIMO, true>(e1, e2, jj, two, ps, pa, rpa, map1, map2, stg);
-#endif
 }
 
 __device__ __forceinline__ float shfl_f(float v, int src) { return __shfl_sync(0xffffffffu, v, src); }
@@ -194,11 +180,23 @@ __device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, 
 template <bool MIMO>
 struct DemodSmem {
     double eqr[DEMOD_GROUPS][64];                                  /* per bin: RN(1 / |H|^2) in binary64 */
-    float stage[DEMOD_GROUPS][(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2) + DEMOD_PAD]; /* one symbol's LLRs per group, deinterleaved; the
-                                                                      first 576 bytes double as the FFT exchange area */
+    float stage[DEMOD_GROUPS][(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2) + DEMOD_PAD]; /* one symbol's LLRs per group, deinterleaved: the
+                                                                      source of the bulk store; the pad holds the dump slot */
+    float2 xch[DEMOD_GROUPS][W_FFT_XCH_FLOAT2];                    /* FFT exchange area of the group (the staging row may still be
+                                                                      draining when the next symbol's FFT runs) */
     float2 tw[8 * 9];                                              /* W64^(g*k1) at [g*9 + k1] */
-    uint16_t smap[DEMOD_GROUPS][(MIMO ? 2 : 1) * (W_MAPLEN + DEMOD_MAPPAD)]; /* the item's deinterleave table(s), each followed by pad entries */
 };
+static_assert(offsetof(W80211Tables, binmap) % 16 == 0, "binmap rows are read as uint4");
+
+/* shared -> global bulk copy by the SM's copy engine, tracked by this thread's bulk async-group (PTX cp.async.bulk) */
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"((uint32_t)__cvta_generic_to_shared(ssrc)), "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+/* until the copy engine has READ the source of every bulk store this thread has issued (the row may be overwritten then) */
+__device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
 template <bool MIMO> /* MIMO = false: one antenna, no two-stream code or registers at all */
 __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_kernel(const W80211Tables* __restrict__ T, int nitems, int npkt, int nant,
@@ -211,7 +209,6 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     DemodSmem<MIMO>& S = *reinterpret_cast<DemodSmem<MIMO>*>(demod_smem_raw);
     auto& stage = S.stage;
     auto& eqr = S.eqr;
-    auto& smap = S.smap;
     const int tid = threadIdx.x;
     const int lane = tid & 31, g = tid & 7, base = lane & ~7, grp = tid >> 3;
     const int w = blockIdx.x * DEMOD_GROUPS + grp;
@@ -248,7 +245,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     const bool any2 = MIMO && __any_sync(0xffffffffu, two);
     const int nloop = __reduce_max_sync(0xffffffffu, nsy);
     float* stg = stage[grp];
-    float2* myx = reinterpret_cast<float2*>(stg); /* used only inside the FFT, before the symbol's LLRs are staged */
+    float2* myx = S.xch[grp];
 
     /* per-item constants: channel of the lane's eight bins (one stream), tables, pilot patterns */
     const float2* H = chan + (size_t)p * chan_stride;
@@ -277,21 +274,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
     const bool ht2 = two && fmt == W80211_F_HT;
     const int nbi = nb == 1 ? 0 : (nb == 2 ? 1 : (nb == 4 ? 2 : (nb == 6 ? 3 : 4)));
     const int tid1 = fmt == W80211_F_L ? nbi : (two ? 9 + nbi : 4 + nbi);
-    {
-        const int nmap = (fmt == W80211_F_L ? 48 : 52) * nb;
-        const uint16_t* gm1 = T->map[tid1];
-        const uint16_t* gm2 = T->map[14 + nbi];
-        for (int k = g; k < nmap; k += 8) {
-            smap[grp][k] = gm1[k];
-            if (MIMO) smap[grp][W_MAPLEN + DEMOD_MAPPAD + k] = gm2[k];
-        }
-        /* bins without data: every bit of them goes to the row's pad slot */
-        smap[grp][W_MAPLEN + g] = (uint16_t)(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2);
-        if (MIMO) smap[grp][2 * W_MAPLEN + DEMOD_MAPPAD + g] = (uint16_t)DEMOD_STAGE;
-        __syncwarp();
-    }
-    const uint16_t* map1 = smap[grp];
-    const uint16_t* map2 = smap[grp] + (MIMO ? W_MAPLEN + DEMOD_MAPPAD : 0);
+    const uint4* map1 = reinterpret_cast<const uint4*>(T->binmap[tid1]) + g;       /* row of bin g + 8 k2 at [8 k2] */
+    const uint4* map2 = reinterpret_cast<const uint4*>(T->binmap[14 + nbi]) + g;
     cf32 R[2][4];
 #pragma unroll
     for (int s2 = 0; s2 < 2; s2++)
@@ -327,17 +311,11 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             e2[k2] = c_make(0.f, 0.f);
             if (!MIMO || !two) {
                 /* every bin, used or not (unused bins divide by 1): no branch in the one-stream path */
-#if DEMOD_NOHOIST
                 /* keep the conversions of H and |H|^2 inside the loop: hoisted, they cost 48 registers */
                 asm volatile("" : "+f"(hh[k2].x), "+f"(hh[k2].y));
-#endif
                 const double hc = hh[k2].x, hd = hh[k2].y;
                 const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
-#if DEMOD_EQHOIST
-                e1[k2] = c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, eqr[grp][i]);
-#else
                 e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, eqr[grp][i]);
-#endif
             } else if (act && jj[k2] >= -1) {
                 {
                     const float4* H4 = reinterpret_cast<const float4*>(H + i * 4);
@@ -351,10 +329,6 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
                 }
             }
         }
-        if (DEMOD_EQHOIST && (!MIMO || !two) && slow_div) {
-#pragma unroll
-            for (int k2 = 0; k2 < 8; k2++) e1[k2] = c_div(c_make(re[k2], im[k2]), hh[k2]);
-        }
         /* the four pilots of each stream, to every lane of the group: bins 7, 21, 43, 57 */
         cf32 a7 = c_make(shfl_f(e1[0].x, base + 7), shfl_f(e1[0].y, base + 7));
         cf32 a21 = c_make(shfl_f(e1[2].x, base + 5), shfl_f(e1[2].y, base + 5));
@@ -367,6 +341,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             b43 = c_make(shfl_f(e2[5].x, base + 3), shfl_f(e2[5].y, base + 3));
             b57 = c_make(shfl_f(e2[7].x, base + 1), shfl_f(e2[7].y, base + 1));
         }
+        cf32 ps = c_make(1.f, 0.f);
+        float pa = 1.f;
         if (act) {
             /* pilot polarity p_{z+n} and the per-symbol rotation of the base pattern (pilotShift) */
             const float P = T->pilot_p[(z + n) % 127];
@@ -396,8 +372,13 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
                 sum = c_add(sum, c_mul(c_scale(c_scale(b43, pl2[0]), P), R[1][0]));
                 sum = c_add(sum, c_mul(c_scale(c_scale(b57, pl2[1]), P), R[1][1]));
             }
-            const cf32 ps = c_conj(sum);
-            const float pa = c_abs(ps);
+            ps = c_conj(sum);
+            pa = c_abs(ps);
+        }
+        /* the previous symbol's row must have left shared memory before this symbol's LLRs go into it */
+        if (g == 0) bulk_store_wait_read();
+        __syncwarp();
+        if (act) {
             /* LLRs through the combined deinterleave / de-parse table into the shared staging block; one instance
              * per modulation so the demapping chain is straight-line code */
             switch (nb) {
@@ -407,28 +388,19 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
             case 6: symbol_llrs<6, MIMO>(e1, e2, jj, two, ps, pa, map1, map2, stg); break;
             default: symbol_llrs<8, MIMO>(e1, e2, jj, two, ps, pa, map1, map2, stg); break;
             }
+            /* every lane's writes become visible to the copy engine (async proxy), then one lane hands it the row: the symbol's
+             * nCBPS floats, 16-byte aligned on both sides (llr_off and nCBPS are multiples of 4 floats) */
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
         __syncwarp();
-        if (act) {
-            /* the symbol's nCBPS floats leave as 16-byte vectors when the rows are 16-byte aligned (128 contiguous bytes per
-             * group and store), else as 8-byte vectors */
-            float2* out2 = reinterpret_cast<float2*>(llr + llr_off + (size_t)n * ncbps);
-            const float2* s2 = reinterpret_cast<const float2*>(stg);
-#if DEMOD_PAD % 4 == 0
-            float4* out4 = reinterpret_cast<float4*>(out2);
-            const float4* s4 = reinterpret_cast<const float4*>(stg);
-            for (int k = g; k < (ncbps >> 2); k += 8) out4[k] = s4[k];
-#else
-            for (int k = g; k < (ncbps >> 1); k += 8) out2[k] = s2[k];
-#endif
-        }
-        __syncwarp();
+        if (act && g == 0) bulk_store(llr + llr_off + (size_t)n * ncbps, stg, (uint32_t)ncbps * 4u);
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             cur0[k] = nx0[k];
             cur1[k] = nx1[k];
         }
     }
+    if (g == 0) bulk_store_wait_read(); /* the block's shared memory must outlive the copy engine's reads */
 }
 
 /* Function attributes are per device: w80211_create() calls this once for the context's device (the current one). */

@@ -113,4 +113,16 @@ void w80211_fill_tables(W80211Tables* t)
             }
         }
     }
+    /* the same maps indexed by FFT bin, eight entries per bin (bits beyond the modulation's and bins without data point at the
+     * first float after the symbol's LLRs): one 16-byte load per bin in demod.cu */
+    for (int m = 0; m < W_NMAPS; m++) {
+        const bool legacy = m < 4;
+        const int nb = legacy ? nbl[m] : nbn[(m - 4) % 5];
+        const int nsd = legacy ? 48 : 52;
+        const int total = (m >= 9 ? 2 : 1) * nsd * nb;
+        for (int i = 0; i < 64; i++) {
+            const int j = legacy ? t->bin_j_l[i] : t->bin_j_nl[i];
+            for (int b = 0; b < 8; b++) t->binmap[m][i][b] = (uint16_t)((j >= 0 && b < nb) ? t->map[m][j * nb + b] : total);
+        }
+    }
 }

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 TAB_DTYPE = np.dtype([("pilot_p", "<f4", 128), ("ltf_nl", "<f4", 64), ("sig_demap", "i1", 64), ("bin_j_l", "i1", 64),
                       ("bin_j_nl", "i1", 64), ("sigb_deint", "u1", 52), ("sigb_int", "u1", 52),
-                      ("map", "<u2", (19, 416)), ("crc_tab", "<u4", (4, 256)), ("crc_x2n", "<u4", 32), ("crc_xpow8", "<u4", 4224), ("scr_seq", "<u4", (128, 8))], align=True)
+                      ("map", "<u2", (19, 416)), ("binmap_align_", "<u2", 4), ("binmap", "<u2", (19, 64, 8)), ("crc_tab", "<u4", (4, 256)), ("crc_x2n", "<u4", 32), ("crc_xpow8", "<u4", 4224), ("scr_seq", "<u4", (128, 8))], align=True)
 
 
 @pytest.fixture(scope="module")
@@ -125,6 +125,22 @@ def test_no_cuda_device_fails_loudly():
         pytest.skip("a GPU is present")
     with pytest.raises(host.W80211Error):
         host.Receiver(0)
+
+
+def test_binmap_is_map_by_fft_bin(tab):
+    """binmap[m][bin][bit] = map[m][j(bin) * nb + bit]; bins without data and bits beyond the modulation's point at the first
+    float after the symbol's LLRs."""
+    nbl, nbn = [1, 2, 4, 6], [1, 2, 4, 6, 8]
+    for m in range(19):
+        legacy = m < 4
+        nb = nbl[m] if legacy else nbn[(m - 4) % 5]
+        binj = tab["bin_j_l"] if legacy else tab["bin_j_nl"]
+        total = (2 if m >= 9 else 1) * (48 if legacy else 52) * nb
+        for i in range(64):
+            j = int(binj[i])
+            for b in range(8):
+                want = int(tab["map"][m][j * nb + b]) if (j >= 0 and b < nb) else total
+                assert int(tab["binmap"][m][i][b]) == want, (m, i, b)
 
 
 def test_pilot_and_ltf(tab, refgr):
