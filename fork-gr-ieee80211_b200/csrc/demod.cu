@@ -21,6 +21,9 @@
 #ifndef DEMOD_MINBLK
 #define DEMOD_MINBLK 8
 #endif
+#ifndef DEMOD_MINBLK2
+#define DEMOD_MINBLK2 4 /* two-antenna variant */
+#endif
 #define DEMOD_GROUPS (DEMOD_THREADS / 8)
 #define DEMOD_SPC W_DEMOD_SPC /* most symbols per work item (one 8-lane group walks them in order) */
 #define DEMOD_STAGE 832    /* floats: largest nCBPS (2 streams of 256-QAM) */
@@ -141,7 +144,7 @@ __device__ __forceinline__ float shfl_f(float v, int src) { return __shfl_sync(0
 __device__ __forceinline__ void load_sym(const float2* __restrict__ src, int g, bool valid, float2* v)
 {
 #pragma unroll
-    for (int n1 = 0; n1 < 8; n1++) v[n1] = valid ? __ldg(&src[8 * n1 + g]) : make_float2(0.f, 0.f);
+    for (int n1 = 0; n1 < 8; n1++) v[n1] = valid ? __ldcs(&src[8 * n1 + g]) : make_float2(0.f, 0.f); /* streamed once: evict-first, the tables and channel blocks stay in L1 */
 }
 
 /* FFT of samples already in registers (same arithmetic as fft64_lane8); the lane's twiddles W64^(g*k1) come from the
@@ -199,7 +202,7 @@ __device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, uint32_
 __device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
 template <bool MIMO> /* MIMO = false: one antenna, no two-stream code or registers at all */
-__global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_kernel(const W80211Tables* __restrict__ T, int nitems, int npkt, int nant,
+__global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MINBLK) demod_kernel(const W80211Tables* __restrict__ T, int nitems, int npkt, int nant,
                                                               const float2* __restrict__ iq0, const float2* __restrict__ iq1,
                                                               const w80211_pkt_in* __restrict__ pkin,
                                                               const w80211_desc* __restrict__ desc, const int* __restrict__ item_prefix,
@@ -305,28 +308,34 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? 4 : DEMOD_MINBLK) demod_
 
         cf32 e1[8], e2[8];
 #pragma unroll
-        for (int k2 = 0; k2 < 8; k2++) {
-            int i = g + 8 * k2;
-            e1[k2] = c_make(0.f, 0.f);
-            e2[k2] = c_make(0.f, 0.f);
-            if (!MIMO || !two) {
-                /* every bin, used or not (unused bins divide by 1): no branch in the one-stream path */
-                /* keep the conversions of H and |H|^2 inside the loop: hoisted, they cost 48 registers */
+        for (int k2 = 0; k2 < 8; k2++) e2[k2] = c_make(0.f, 0.f);
+        if (!MIMO || !two) {
+#pragma unroll
+            for (int k2 = 0; k2 < 8; k2++) {
+                const int i = g + 8 * k2;
+                /* every bin, used or not (unused bins divide by 1): no branch in the one-stream path.
+                 * keep the conversions of H and |H|^2 inside the loop: hoisted, they cost 48 registers */
                 asm volatile("" : "+f"(hh[k2].x), "+f"(hh[k2].y));
                 const double hc = hh[k2].x, hd = hh[k2].y;
                 const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
                 e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, eqr[grp][i]);
-            } else if (act && jj[k2] >= -1) {
-                {
-                    const float4* H4 = reinterpret_cast<const float4*>(H + i * 4);
-                    const float4* I4 = reinterpret_cast<const float4*>(H + 256 + i * 4);
-                    float4 ha = __ldg(H4), hb = __ldg(H4 + 1), ia = __ldg(I4), ib = __ldg(I4 + 1);
-                    cf32 y1 = c_make(re[k2], im[k2]), y2 = c_make(re2[k2], im2[k2]);
-                    cf32 t1 = c_add(c_mul(y1, c_make(ha.x, -ha.y)), c_mul(y2, c_make(ha.z, -ha.w)));
-                    cf32 t2 = c_add(c_mul(y1, c_make(hb.x, -hb.y)), c_mul(y2, c_make(hb.z, -hb.w)));
-                    e1[k2] = c_add(c_mul(t1, c_make(ia.x, ia.y)), c_mul(t2, c_make(ib.x, ib.y)));
-                    e2[k2] = c_add(c_mul(t1, c_make(ia.z, ia.w)), c_mul(t2, c_make(ib.z, ib.w)));
-                }
+            }
+        } else {
+            /* two streams: H^H y, then the inverse of H^H H (demod2_impl.cc:471-630), every bin and every lane alike -- no
+             * condition between the loads and the loop head, so they are issued bins ahead of their use (the results of unused
+             * bins and of lanes past their item's end go nowhere: their table rows point at the dump slot, nothing is stored
+             * for an inactive lane) */
+#pragma unroll
+            for (int k2 = 0; k2 < 8; k2++) {
+                const int i = g + 8 * k2;
+                const float4* H4 = reinterpret_cast<const float4*>(H + i * 4);
+                const float4* I4 = reinterpret_cast<const float4*>(H + 256 + i * 4);
+                const float4 ha = __ldg(H4), hb = __ldg(H4 + 1), ia = __ldg(I4), ib = __ldg(I4 + 1);
+                const cf32 y1 = c_make(re[k2], im[k2]), y2 = c_make(re2[k2], im2[k2]);
+                const cf32 t1 = c_add(c_mul(y1, c_make(ha.x, -ha.y)), c_mul(y2, c_make(ha.z, -ha.w)));
+                const cf32 t2 = c_add(c_mul(y1, c_make(hb.x, -hb.y)), c_mul(y2, c_make(hb.z, -hb.w)));
+                e1[k2] = c_add(c_mul(t1, c_make(ia.x, ia.y)), c_mul(t2, c_make(ib.x, ib.y)));
+                e2[k2] = c_add(c_mul(t1, c_make(ia.z, ia.w)), c_mul(t2, c_make(ib.z, ib.w)));
             }
         }
         /* the four pilots of each stream, to every lane of the group: bins 7, 21, 43, 57 */
