@@ -104,8 +104,9 @@ struct SigStage {
     DevBuf iq[2], syncs, res, chan_all, acc, out_iq[2], out_chan;
     PinBuf h_res, h_acc;
     /* detection stage */
-    DevBuf det_ac, det_conj, det_sig, det_cnt, det_starts, det_ends, det_sorted, det_tmp, det_ev, det_res;
+    DevBuf det_ac, det_conj, det_sig, det_cnt, det_starts, det_ends, det_tmp, det_ev, det_res;
     PinBuf h_edges, h_ev, h_dres;
+    unsigned int edge_cap = 4096; /* run edges the lists are sized for: one and a half times what the last call found */
 };
 
 } // namespace
@@ -880,7 +881,7 @@ void w80211_destroy(w80211_ctx* ctx)
     {
         SigStage& g = ctx->sig;
         DevBuf* db[] = {&g.iq[0], &g.iq[1], &g.syncs, &g.res, &g.chan_all, &g.acc, &g.out_iq[0], &g.out_iq[1], &g.out_chan,
-                        &g.det_ac, &g.det_conj, &g.det_sig, &g.det_cnt, &g.det_starts, &g.det_ends, &g.det_sorted, &g.det_tmp, &g.det_ev, &g.det_res};
+                        &g.det_ac, &g.det_conj, &g.det_sig, &g.det_cnt, &g.det_starts, &g.det_ends, &g.det_tmp, &g.det_ev, &g.det_res};
         for (DevBuf* b : db)
             if (b->p) cudaFree(b->p);
         if (g.h_res.p) cudaFreeHost(g.h_res.p);
@@ -1162,35 +1163,36 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
         d_cj = (const float2*)g.det_conj.p;
         d_sg = (const float2*)g.det_sig.p;
     }
-    /* ---- runs of preac > 0.3: count the edges, then list them */
+    /* ---- runs of preac > 0.3: both edge lists in ascending order, counts and lists in one round trip.  The lists are sized
+     * from what the previous call needed; a call that finds more edges than that grows them and runs the three small kernels
+     * once more. */
+    const int nblk = w_edges_blocks((unsigned long long)n);
     RS(dev_reserve(ctx, g.det_cnt, 16));
-    RS(pin_reserve(ctx, g.h_edges, 16));
-    CK(cudaMemsetAsync(g.det_cnt.p, 0, 16, st));
-    w_launch_run_edges(st, d_ac, (unsigned long long)n, st0.n_plateau > 0, 0, (unsigned int*)g.det_cnt.p, nullptr, nullptr);
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(g.h_edges.p, g.det_cnt.p, 16, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    const unsigned int ns = ((unsigned int*)g.h_edges.p)[0], ne = ((unsigned int*)g.h_edges.p)[1];
-    RS(dev_reserve(ctx, g.det_starts, (size_t)ns * 4 + 16));
-    RS(dev_reserve(ctx, g.det_ends, (size_t)ne * 4 + 16));
-    CK(cudaMemsetAsync(g.det_cnt.p, 0, 16, st));
-    w_launch_run_edges(st, d_ac, (unsigned long long)n, st0.n_plateau > 0, std::max(ns, ne), (unsigned int*)g.det_cnt.p,
-                       (unsigned int*)g.det_starts.p, (unsigned int*)g.det_ends.p);
-    CK(cudaGetLastError());
-    RS(pin_reserve(ctx, g.h_edges, (size_t)(ns + ne) * 4 + 16));
-    unsigned int* hs = (unsigned int*)g.h_edges.p;
-    unsigned int* he = hs + ns;
-    {
-        const size_t tb = w_sort_u32_temp_bytes((int)std::max(ns, ne));
-        RS(dev_reserve(ctx, g.det_tmp, tb + 16));
-        RS(dev_reserve(ctx, g.det_sorted, (size_t)(ns + ne) * 4 + 16));
-        unsigned int* ds = (unsigned int*)g.det_sorted.p;
-        w_sort_u32(st, g.det_tmp.p, tb, (const unsigned int*)g.det_starts.p, ds, (int)ns);
-        w_sort_u32(st, g.det_tmp.p, tb, (const unsigned int*)g.det_ends.p, ds + ns, (int)ne);
+    RS(dev_reserve(ctx, g.det_tmp, (size_t)nblk * 2 * sizeof(uint2) + 16));
+    unsigned int cap = std::max(g.edge_cap, 4096u), ns = 0, ne = 0;
+    unsigned int *hs = nullptr, *he = nullptr;
+    for (int attempt = 0;; attempt++) {
+        RS(dev_reserve(ctx, g.det_starts, (size_t)cap * 4 + 16));
+        RS(dev_reserve(ctx, g.det_ends, (size_t)cap * 4 + 16));
+        RS(pin_reserve(ctx, g.h_edges, (size_t)cap * 8 + 16));
+        CK(cudaMemsetAsync(g.det_cnt.p, 0, 16, st));
+        w_launch_run_edges(st, d_ac, (unsigned long long)n, st0.n_plateau > 0, cap, (unsigned int*)g.det_cnt.p, (unsigned int*)g.det_starts.p,
+                           (unsigned int*)g.det_ends.p, g.det_tmp.p);
         CK(cudaGetLastError());
-        if (ns + ne) CK(cudaMemcpyAsync(hs, ds, (size_t)(ns + ne) * 4, cudaMemcpyDeviceToHost, st));
+        unsigned int* hc = (unsigned int*)g.h_edges.p;
+        hs = hc + 4;
+        he = hs + cap;
+        CK(cudaMemcpyAsync(hc, g.det_cnt.p, 16, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(hs, g.det_starts.p, (size_t)cap * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(he, g.det_ends.p, (size_t)cap * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        ns = hc[0];
+        ne = hc[1];
+        if (std::max(ns, ne) <= cap) break;
+        if (attempt) return fail(ctx, W80211_E_STATE, "detect_batch: edge count changed between two passes");
+        cap = std::max(ns, ne) + 16;
     }
-    CK(cudaStreamSynchronize(st));
+    g.edge_cap = std::max(ns, ne) + std::max(ns, ne) / 2 + 16;
     const auto tt1 = tnow();
     struct Run {
         long long s, e; /* [s, e): s < 0 when the run began before this buffer, e = n when it is still open */
@@ -1307,7 +1309,7 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
     }
     s1.sync_skip = (int32_t)std::max(0ll, pos - next);
     out->state = next > 0 ? s1 : st0; /* next = 0: nothing was consumed */
-    ctx->stats.kernel_launches += 3;
+    ctx->stats.kernel_launches += 4;
     return W80211_OK;
 }
 

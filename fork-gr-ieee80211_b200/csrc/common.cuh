@@ -214,12 +214,11 @@ struct w_det_result {
     int valid, mindex;
     float rad, snr, rssi;
 };
+int w_edges_blocks(unsigned long long n);
 void w_launch_run_edges(cudaStream_t st, const float* ac, unsigned long long n, int prev_above0, unsigned int cap,
-                        unsigned int* counters, unsigned int* starts, unsigned int* ends);
+                        unsigned int* counters, unsigned int* starts, unsigned int* ends, void* blk);
 void w_launch_sync_events(cudaStream_t st, int nev, const w_det_event* ev, const float* ac, const float2* conj, const float2* sig,
                           float conj_ac0, float2 conj0, w_det_result* res);
-size_t w_sort_u32_temp_bytes(int n);
-void w_sort_u32(cudaStream_t st, void* temp, size_t temp_bytes, const unsigned int* in, unsigned int* out, int n);
 void w_launch_presiso(cudaStream_t st, const float2* x, unsigned long long n, float* ac, float2* cj);
 void w_launch_lsig(cudaStream_t st, const W80211Tables* tab, int nsync, const w80211_sync* syncs, const float2* iq0,
                    unsigned long long nsamples, int4* res, float2* chan_all);

@@ -2,7 +2,8 @@
  * block (lib/trigger_impl.cc:60-117) and sync block (lib/sync_impl.cc:61-196).
  *
  *   run_edges_kernel   one thread per sample: where runs of preac > 0.3 begin and end (the only thing the trigger's
- *                      plateau counter, its running maximum and its flags depend on).  The few edges go to two lists.
+ *                      plateau counter, its running maximum and its flags depend on).  The few edges go to two lists in
+ *                      ascending position (count per block, scan, write at offset + rank: no sort, no library kernel).
  *   (host)             w80211_detect_batch walks the runs in order: plateau > 20 -> 80-sample countdown -> trigger flag,
  *                      one countdown at a time, one per run; then the sync block's IDLE / SYNC alternation (a trigger
  *                      inside the 111 samples a SYNC pass consumes is never seen).
@@ -14,25 +15,136 @@
  * Every per-trigger result depends on at most a few hundred samples, so a thread per trigger keeps the reference's
  * operation order (bit-exact sums) and the batch supplies the parallelism.
  */
-#include <cub/device/device_radix_sort.cuh>
 #include "common.cuh"
 
 __device__ __forceinline__ bool above_thr(float v) { return v > 0.3f; }
 
-__global__ void __launch_bounds__(256) run_edges_kernel(const float* __restrict__ ac, unsigned long long n, int prev_above0,
-                                                        unsigned int cap, unsigned int* __restrict__ counters,
-                                                        unsigned int* __restrict__ starts, unsigned int* __restrict__ ends)
+/* Edges of the runs of preac > 0.3, listed in ascending position without a sort: a block covers EDGE_TILES x EDGE_BLOCK
+ * consecutive samples; pass 1 (WRITE = false) counts the block's starts and ends, a one-block scan turns the counts into
+ * offsets, pass 2 (WRITE = true) finds the same edges again and stores each at offset + its rank inside the block (ballot
+ * prefix inside a warp, warp totals through shared memory) -- ranks follow positions, so both lists come out ordered. */
+#define EDGE_BLOCK 1024
+#define EDGE_TILES 4
+template <bool WRITE>
+__global__ void __launch_bounds__(EDGE_BLOCK) run_edges_kernel(const float* __restrict__ ac, unsigned long long n, int prev_above0,
+                                                               uint2* __restrict__ blk_cnt, const uint2* __restrict__ blk_off,
+                                                               unsigned int cap, unsigned int* __restrict__ starts,
+                                                               unsigned int* __restrict__ ends, unsigned int* __restrict__ counters)
 {
-    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const bool a = above_thr(__ldg(ac + i));
-    const bool b = i ? above_thr(__ldg(ac + i - 1)) : (prev_above0 != 0);
-    if (a && !b) {
-        unsigned int k = atomicAdd(&counters[0], 1u);
-        if (k < cap) starts[k] = (unsigned int)i;
-    } else if (!a && b) {
-        unsigned int k = atomicAdd(&counters[1], 1u);
-        if (k < cap) ends[k] = (unsigned int)i;
+    __shared__ unsigned int wtot[2][32];
+    __shared__ unsigned int run[2], tile_tot[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned long long base = (unsigned long long)blockIdx.x * (EDGE_BLOCK * EDGE_TILES);
+    if (tid == 0) {
+        run[0] = WRITE ? blk_off[blockIdx.x].x : 0u;
+        run[1] = WRITE ? blk_off[blockIdx.x].y : 0u;
+    }
+    __syncthreads();
+    for (int t = 0; t < EDGE_TILES; t++) {
+        const unsigned long long i = base + (unsigned long long)t * EDGE_BLOCK + tid;
+        bool is_s = false, is_e = false;
+        if (i < n) {
+            const bool a = above_thr(__ldg(ac + i));
+            const bool b = i ? above_thr(__ldg(ac + i - 1)) : (prev_above0 != 0);
+            is_s = a && !b;
+            is_e = !a && b;
+        }
+        const unsigned int bs = __ballot_sync(0xffffffffu, is_s), be = __ballot_sync(0xffffffffu, is_e);
+        if (lane == 0) {
+            wtot[0][warp] = __popc(bs);
+            wtot[1][warp] = __popc(be);
+        }
+        __syncthreads();
+        if (warp == 0) { /* exclusive scan of the 32 warp totals, both lists; lane 31 ends up with the tile's totals */
+            const unsigned int vs = wtot[0][lane], ve = wtot[1][lane];
+            unsigned int xs = vs, xe = ve;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned int us = __shfl_up_sync(0xffffffffu, xs, d), ue = __shfl_up_sync(0xffffffffu, xe, d);
+                if (lane >= d) {
+                    xs += us;
+                    xe += ue;
+                }
+            }
+            wtot[0][lane] = xs - vs;
+            wtot[1][lane] = xe - ve;
+            if (lane == 31) {
+                tile_tot[0] = xs;
+                tile_tot[1] = xe;
+            }
+        }
+        __syncthreads();
+        if (WRITE) {
+            if (is_s) {
+                const unsigned int k = run[0] + wtot[0][warp] + __popc(bs & ((1u << lane) - 1u));
+                if (k < cap) starts[k] = (unsigned int)i;
+            }
+            if (is_e) {
+                const unsigned int k = run[1] + wtot[1][warp] + __popc(be & ((1u << lane) - 1u));
+                if (k < cap) ends[k] = (unsigned int)i;
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            run[0] += tile_tot[0];
+            run[1] += tile_tot[1];
+        }
+    }
+    __syncthreads();
+    if (!WRITE && tid == 0) {
+        blk_cnt[blockIdx.x] = make_uint2(run[0], run[1]);
+        if (run[0]) atomicAdd(&counters[0], run[0]);
+        if (run[1]) atomicAdd(&counters[1], run[1]);
+    }
+}
+
+/* exclusive scan of the per-block (starts, ends) counts: one block, each thread a contiguous chunk */
+__global__ void __launch_bounds__(1024) edges_scan_kernel(const uint2* __restrict__ cnt, uint2* __restrict__ off, int nblk)
+{
+    __shared__ unsigned int ws[2][32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (nblk + 1023) / 1024, lo = tid * per, hi = min(nblk, lo + per);
+    unsigned int s0 = 0, s1 = 0;
+    for (int k = lo; k < hi; k++) {
+        const uint2 c = cnt[k];
+        s0 += c.x;
+        s1 += c.y;
+    }
+    unsigned int x0 = s0, x1 = s1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int u0 = __shfl_up_sync(0xffffffffu, x0, d), u1 = __shfl_up_sync(0xffffffffu, x1, d);
+        if (lane >= d) {
+            x0 += u0;
+            x1 += u1;
+        }
+    }
+    if (lane == 31) {
+        ws[0][warp] = x0;
+        ws[1][warp] = x1;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const unsigned int v0 = ws[0][lane], v1 = ws[1][lane];
+        unsigned int y0 = v0, y1 = v1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned int u0 = __shfl_up_sync(0xffffffffu, y0, d), u1 = __shfl_up_sync(0xffffffffu, y1, d);
+            if (lane >= d) {
+                y0 += u0;
+                y1 += u1;
+            }
+        }
+        ws[0][lane] = y0 - v0;
+        ws[1][lane] = y1 - v1;
+    }
+    __syncthreads();
+    unsigned int o0 = ws[0][warp] + x0 - s0, o1 = ws[1][warp] + x1 - s1;
+    for (int k = lo; k < hi; k++) {
+        off[k] = make_uint2(o0, o1);
+        const uint2 c = cnt[k];
+        o0 += c.x;
+        o1 += c.y;
     }
 }
 
@@ -155,12 +267,20 @@ __global__ void __launch_bounds__(64) sync_event_kernel(int nev, const w_det_eve
     res[k] = r;
 }
 
+int w_edges_blocks(unsigned long long n) { return (int)((n + EDGE_BLOCK * EDGE_TILES - 1) / (EDGE_BLOCK * EDGE_TILES)); }
+
+/* counts -> offsets -> ordered lists, all on `st`; counters[0..1] = number of starts / ends (may exceed cap: the caller grows
+ * the lists and calls again).  blk: 2 x w_edges_blocks(n) uint2 of scratch. */
 void w_launch_run_edges(cudaStream_t st, const float* ac, unsigned long long n, int prev_above0, unsigned int cap,
-                        unsigned int* counters, unsigned int* starts, unsigned int* ends)
+                        unsigned int* counters, unsigned int* starts, unsigned int* ends, void* blk)
 {
     if (n == 0) return;
-    const unsigned long long blocks = (n + 255) / 256;
-    run_edges_kernel<<<(unsigned int)blocks, 256, 0, st>>>(ac, n, prev_above0, cap, counters, starts, ends);
+    const int nb = w_edges_blocks(n);
+    uint2* cnt = (uint2*)blk;
+    uint2* off = cnt + nb;
+    run_edges_kernel<false><<<nb, EDGE_BLOCK, 0, st>>>(ac, n, prev_above0, cnt, nullptr, 0, nullptr, nullptr, counters);
+    edges_scan_kernel<<<1, 1024, 0, st>>>(cnt, off, nb);
+    run_edges_kernel<true><<<nb, EDGE_BLOCK, 0, st>>>(ac, n, prev_above0, nullptr, off, cap, starts, ends, nullptr);
 }
 
 void w_launch_sync_events(cudaStream_t st, int nev, const w_det_event* ev, const float* ac, const float2* conj, const float2* sig,
@@ -230,16 +350,4 @@ void w_launch_presiso(cudaStream_t st, const float2* x, unsigned long long n, fl
 {
     if (n == 0) return;
     presiso_kernel<<<(unsigned int)((n + PRE_TILE - 1) / PRE_TILE), PRE_THREADS, 0, st>>>(x, n, ac, cj);
-}
-
-/* the edge lists come out of the atomics in arbitrary order: radix sort them on the device (a few 10^4 keys) */
-size_t w_sort_u32_temp_bytes(int n)
-{
-    size_t b = 0;
-    cub::DeviceRadixSort::SortKeys(nullptr, b, (const unsigned int*)nullptr, (unsigned int*)nullptr, n);
-    return b;
-}
-void w_sort_u32(cudaStream_t st, void* temp, size_t temp_bytes, const unsigned int* in, unsigned int* out, int n)
-{
-    if (n > 0) cub::DeviceRadixSort::SortKeys(temp, temp_bytes, in, out, n, 0, 32, st);
 }

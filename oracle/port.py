@@ -26,6 +26,8 @@ def lib():
         L.port_chan_nl.argtypes = [vp, vp]
         L.port_chan_nl.restype = None
         L.port_demod_data.argtypes = [ci, ci, ci, ci, vp, vp, vp]
+        L.port_presiso.argtypes = [vp, C.c_long, ci, vp, vp]
+        L.port_presiso.restype = None
         _lib = L
     return _lib
 
@@ -92,3 +94,14 @@ def demod_packet(post, chan_legacy, fmt, nbpscs, nsym, short_gi=False):
     if r < 0:
         raise ValueError("port_demod_data: bad parameters")
     return out
+
+
+def presiso(x, chunk=0):
+    """examples/presiso.grc with GNU Radio's sequential binary32 running sums (oracle/port/presiso_port.c): chunk = 0 carries
+    the sums over the whole stream (3.9 / 3.10), chunk > 0 re-makes them every `chunk` outputs (one work() call of 3.7 / 3.8).
+    -> (preac float32[n], preconj complex64[n])"""
+    x = np.ascontiguousarray(x, np.complex64)
+    ac = np.zeros(len(x), np.float32)
+    cj = np.zeros(len(x), np.complex64)
+    lib().port_presiso(x.ctypes.data, len(x), int(chunk), ac.ctypes.data, cj.ctypes.data)
+    return ac, cj

@@ -125,3 +125,27 @@ def test_presiso_on_the_gpu(refgr, rx):
     assert len(mine) == len(ref) == len(pos)
     for s, (o, t) in zip(mine, ref):
         assert abs(int(s["pos"]) - o) <= 1 and abs(float(s["rad"]) - t["rad"]) <= 1e-4
+
+
+@pytest.mark.parametrize("chunk", [0, 4000, 1537])
+def test_presiso_against_gnuradios_running_sums(refgr, rx, chunk):
+    """The stock GNU Radio blocks behind presiso.grc keep sequential binary32 running sums (carried over the whole stream in
+    3.10, re-made at every work() call of at most max_iter = 4000 outputs in 3.8: oracle/port/presiso_port.c).  The GPU stage
+    stays within 1e-4 of either, and the reference's trigger + sync blocks take the same decisions on either side's streams:
+    the same flags at the same samples with the same rssi, rad and snr to the tolerance of same_flags."""
+    from oracle import port
+    bs, raw, pos, rad = stream_of(41, noise=0.05, gap=450)
+    x = raw[0]
+    ac_gr, cj_gr = port.presiso(x, chunk)
+    ac, cj = rx.presiso(x)
+    ok = np.isfinite(ac_gr) & (np.arange(len(x)) >= 80)
+    # GNU Radio's carried binary32 sums drift by a few ulp of the largest value they have held: the floor of the comparison
+    assert np.all(np.abs(cj[ok] - cj_gr[ok]) <= 1e-4 * np.abs(cj_gr[ok]) + 2e-6 * np.abs(cj_gr).max())
+    busy = ok & (np.abs(cj_gr) > 1e-2 * np.abs(cj_gr).max())
+    assert np.all(np.abs(ac[busy] - ac_gr[busy]) <= 1e-3 * np.maximum(ac_gr[busy], 1e-2))
+    ref, _, _ = ref_detect(refgr, ac_gr, cj_gr, x)
+    mine = rx.detect(ac, cj, x)["syncs"]
+    assert len(mine) == len(ref) == len(pos)
+    for s, (o, t) in zip(mine, ref):
+        assert int(s["pos"]) == o
+        assert abs(float(s["rad"]) - t["rad"]) <= 1e-4 and abs(float(s["snr"]) - t["snr"]) <= 1e-2 * max(1.0, abs(t["snr"]))

@@ -84,3 +84,26 @@ def test_demod_port_matches_reference_demod(refgr, fmt, mcs, length, sgi):
         nsym = int(r["total"]) // (nsd * nb)
         got = port.demod_packet(b["post"][0][p], b["chan"][p], fmt, nb, nsym, short_gi=sgi)
         assert np.array_equal(got, r["llr"][: len(got)]) and len(got) == int(r["total"])
+
+
+def test_presiso_port_variants_agree_with_a_binary64_evaluation(refgr):
+    """oracle/port/presiso_port.c (GNU Radio's binary32 running sums, carried or re-made per work() call) against the
+    binary64 evaluation of tests/util.py, and the reference's trigger + sync blocks fed each: same flags (CPU only)."""
+    import w80211rx
+    from util import build_stream, presiso
+    gp, g = w80211rx.gen_ppdu, w80211rx.gen
+    bs = [gp.gen_batch(g.F_HT, 4, 1, 200, 3, snr_db=25, seed=51), gp.gen_batch(g.F_L, 2, 1, 90, 3, snr_db=25, seed=52)]
+    raw, pos, rad = build_stream(bs, [0.01, -0.015], gap=500, noise=0.05, seed=5)
+    x = raw[0]
+    ac64, cj64 = presiso(x)
+    flags = []
+    for chunk in (0, 4000, 777):
+        ac, cj = port.presiso(x, chunk)
+        ok = np.isfinite(ac64) & (np.arange(len(x)) >= 80)
+        # a carried binary32 sum drifts by a few ulp of the largest value it has held: the floor of the comparison
+        assert np.all(np.abs(cj[ok] - cj64[ok]) <= 1e-4 * np.abs(cj64[ok]) + 2e-6 * np.abs(cj64).max())
+        busy = ok & (np.abs(cj64) > 1e-2 * np.abs(cj64).max())
+        assert np.all(np.abs(ac[busy] - ac64[busy]) <= 1e-3 * np.maximum(ac64[busy], 1e-2))
+        sy = refgr.run_sync(refgr.run_trigger(ac), cj, x)
+        flags.append([o for o, _ in sy.tags()])
+    assert flags[0] == flags[1] == flags[2] and len(flags[0]) == len(pos)
