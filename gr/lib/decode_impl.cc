@@ -453,7 +453,7 @@ int decode_impl::general_work(int /*noutput_items*/,
             const long n = std::min<long>(navail - consumed, d_left);
             const long ncopy = std::min(n, d_copy_left);
             if (ncopy > 0) {
-                std::memcpy(b.llr.data() + b.fill, in + consumed, (size_t)ncopy * sizeof(float));
+                stream_copy(b.llr.data() + b.fill, in + consumed, (size_t)ncopy * sizeof(float));
                 b.fill += (uint64_t)ncopy;
                 d_copy_left -= ncopy;
                 if (d_copy_left == 0) b.ncomplete++;

@@ -7,6 +7,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#if defined(__x86_64__) && defined(__GNUC__)
+#include <immintrin.h>
+#endif
 
 namespace gr {
 namespace ieee80211 {
@@ -47,6 +50,46 @@ void staged_array<T>::release()
 
 template class staged_array<float>;
 template class staged_array<unsigned char>;
+
+/* ------------------------------------------------------------------ stream_copy */
+/* Samples go from the scheduler's buffer into page-locked staging exactly once and are next read by the GPU's copy engine, not
+ * by this core: written with non-temporal stores they neither cost a read-for-ownership of the destination line nor push the
+ * source out of the cache.  AVX2 when the CPU has it (checked at run time), memcpy otherwise. */
+#if defined(__x86_64__) && defined(__GNUC__)
+__attribute__((target("avx2"))) static void stream_copy_avx2(unsigned char* d, const unsigned char* s, size_t n)
+{
+    const size_t head = (32 - (reinterpret_cast<uintptr_t>(d) & 31)) & 31;
+    if (head >= n) {
+        std::memcpy(d, s, n);
+        return;
+    }
+    std::memcpy(d, s, head);
+    d += head, s += head, n -= head;
+    size_t i = 0;
+    for (; i + 128 <= n; i += 128) {
+        const __m256i a = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s + i));
+        const __m256i b = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s + i + 32));
+        const __m256i c = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s + i + 64));
+        const __m256i e = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s + i + 96));
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(d + i), a);
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(d + i + 32), b);
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(d + i + 64), c);
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(d + i + 96), e);
+    }
+    _mm_sfence();
+    if (i < n) std::memcpy(d + i, s + i, n - i);
+}
+void stream_copy(void* dst, const void* src, size_t bytes)
+{
+    static const bool avx2 = __builtin_cpu_supports("avx2") && std::getenv("W80211_NO_STREAM_COPY") == nullptr;
+    if (avx2 && bytes >= 4096)
+        stream_copy_avx2(static_cast<unsigned char*>(dst), static_cast<const unsigned char*>(src), bytes);
+    else
+        std::memcpy(dst, src, bytes);
+}
+#else
+void stream_copy(void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); }
+#endif
 
 /* ------------------------------------------------------------------ rx_env */
 static long env_long(const char* name, long dflt)
@@ -262,7 +305,7 @@ int demod_core::ingest(int base, int navail, gr_vector_const_void_star& input_it
         if (ncopy > 0) {
             for (int a = 0; a < d_nant; a++) {
                 const float* src = static_cast<const float*>(input_items[a]) + (size_t)consumed * 2;
-                std::memcpy(b.iq[a].data() + (size_t)b.fill * 2, src, (size_t)ncopy * 8);
+                stream_copy(b.iq[a].data() + (size_t)b.fill * 2, src, (size_t)ncopy * 8);
             }
             b.fill += (uint64_t)ncopy;
             d_copy_left -= ncopy;

@@ -65,6 +65,9 @@ private:
     bool d_pinned;
 };
 
+/* copy into page-locked staging that the CPU will not read again (non-temporal stores where the CPU has AVX2) */
+void stream_copy(void* dst, const void* src, size_t bytes);
+
 enum llr_handoff { HANDOFF_AUTO = 0, HANDOFF_HOST, HANDOFF_BOTH, HANDOFF_DEVICE };
 
 /* environment knobs shared by the three blocks */
