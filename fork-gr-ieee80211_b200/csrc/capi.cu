@@ -275,6 +275,7 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     /* One pass over the descriptors (12 MB for a full batch; the later loops only touch a 4-byte key per packet): LLR
      * layout, symbol prefix sums, and the packets to decode with their sort key (code rate ascending, trellis descending). */
     uint64_t off = 0;
+    static const int spc2 = getenv("W80211_SPC2") ? std::max(1, atoi(getenv("W80211_SPC2"))) : W_DEMOD_SPC2;
     std::vector<int>& symprefix = s.v_symprefix;
     symprefix.assign((size_t)npkt + 1, 0);
     std::vector<int>& dec = s.v_dec;
@@ -296,7 +297,10 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
         } else if (assign_llr) {
             d.llr_off = -1;
         }
-        symprefix[p + 1] = symprefix[p] + (nsym + W_DEMOD_SPC - 1) / W_DEMOD_SPC; /* demod work items: runs of W_DEMOD_SPC symbols */
+        /* demod work items: runs of at most spc symbols of one packet.  Two-stream packets take short runs, so that the eight
+         * groups of a block mostly work on one packet and share its 4 KB of channel matrices in L1 */
+        const int spc = (s.nant == 2 && d.nss == 2) ? spc2 : W_DEMOD_SPC;
+        symprefix[p + 1] = symprefix[p] + (nsym + spc - 1) / spc;
         if (!do_decode || d.status != W80211_ST_OK) continue;
         /* decode_impl.cc:93: len > 4095 or trellis > 32782 -> skipped */
         if (d.len > W80211_B_MAX || d.len < 0 || d.trellis > W80211_T_MAX || d.trellis <= 0) continue;

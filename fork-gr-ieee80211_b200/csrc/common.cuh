@@ -24,6 +24,9 @@
 #ifndef W_DEMOD_SPC
 #define W_DEMOD_SPC 36 /* most symbols per demod work item (one 8-lane group walks them in order); the host plan counts items with it */
 #endif
+#ifndef W_DEMOD_SPC2
+#define W_DEMOD_SPC2 16 /* the same for two-stream packets (W80211_SPC2 in the environment overrides it: tuning) */
+#endif
 #define W_XPOW8 4224
 
 /* Constant tables, generated on the host from the 802.11 formulas (tables.cc)
