@@ -770,7 +770,7 @@ def main():
     ap.add_argument("--mpdu-len", type=int, default=4088, help="profiling only: shorter C4 packets; the reported workload is the default")
     ap.add_argument("--ref-packets", type=int, default=512, help="--impl reference: packets per core and step")
     ap.add_argument("--cpu-packets", type=int, default=128, help="packets per core of the cpu_baseline sample inside the GPU arm")
-    ap.add_argument("--blocks-packets", type=int, default=4096, help="packets of the e2e_blocks leg")
+    ap.add_argument("--blocks-packets", type=int, default=8192, help="packets of the e2e_blocks leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--config", default="C4", choices=["C2", "C3", "C4", "C5", "T12", "T23"],
                     help="tuning runs (with --resident-only): another configuration of BASELINE.json as the main workload; the benchmark's is C4 "

@@ -127,6 +127,7 @@ struct w80211_ctx {
     /* LLR buffers this context has handed out as leases come back here when they retire (under g_lease_mu) */
     std::vector<DevBuf> llr_free;
     std::deque<uint64_t> leases; /* handles exported by this context, oldest first */
+    size_t lease_bytes = (size_t)4 << 30; /* W80211_LEASE_BYTES: device memory the leases beyond the newest six may hold */
     Slot slots[4];
     SigStage sig;
     w80211_stats stats = {};
@@ -838,6 +839,7 @@ int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
     ctx->nslots = cfg && cfg->nslots > 0 ? std::min(cfg->nslots, 4) : 2;
     ctx->vit_mode = cfg ? (cfg->flags & W80211_CFG_VITERBI_MASK) : W80211_CFG_VITERBI_AUTO;
     if (const char* e = getenv("W80211_WARP_MAX_PKTS")) ctx->warp_max_pkts = atoi(e);
+    if (const char* e = getenv("W80211_LEASE_BYTES")) ctx->lease_bytes = (size_t)strtoull(e, nullptr, 10);
     if (ctx->device < 0 || ctx->device >= ndev || cudaSetDevice(ctx->device) != cudaSuccess) {
         delete ctx;
         return W80211_E_ARG;
@@ -1052,9 +1054,17 @@ int w80211_llr_export(w80211_ctx* ctx, int slot, uint64_t* handle)
     if (s.busy || !s.did_demod) return fail(ctx, W80211_E_STATE, "llr_export: slot %d holds no collected demod batch", slot);
     if (!s.llr.p || s.n_llr == 0) return fail(ctx, W80211_E_STATE, "llr_export: the batch in slot %d produced no LLRs", slot);
     std::lock_guard<std::mutex> lk(g_lease_mu);
-    /* keep the newest W80211_LEASES_KEPT - 1 and this one; older ones retire (a decode batch still reading one keeps its
-     * memory alive until it collects) */
-    while ((int)ctx->leases.size() >= W80211_LEASES_KEPT) {
+    /* the newest W80211_LEASES_KEPT always stay; older ones stay too while the context's leases are few and small (a consumer
+     * may lag by whatever the edge between the two blocks buffers) and retire oldest first beyond that (a decode batch still
+     * reading one keeps its memory alive until it collects) */
+    for (;;) {
+        size_t held = s.llr.cap;
+        for (uint64_t id : ctx->leases) {
+            auto it = g_leases.find(id);
+            if (it != g_leases.end()) held += it->second.buf.cap;
+        }
+        const size_t n = ctx->leases.size() + 1;
+        if (n <= (size_t)W80211_LEASES_KEPT || (n <= 64 && held <= ctx->lease_bytes)) break;
         const uint64_t old = ctx->leases.front();
         ctx->leases.pop_front();
         auto it = g_leases.find(old);

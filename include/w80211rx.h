@@ -329,8 +329,10 @@ int w80211_rx_poll(w80211_ctx* ctx, int slot);
  * demod_submit() is rx_submit() without the decode half: descriptors (and, with out->want_llr, the LLR stream) come back
  * at w80211_rx_collect().  After that collect the batch's LLRs are still in HBM; w80211_llr_export() detaches them from the
  * slot as a LEASE, a process-wide handle another context on the same GPU -- the decode block's -- can decode from without
- * the 43 LLRs per payload byte crossing PCIe twice.  A producer keeps its W80211_LEASES_KEPT newest leases; exporting one
- * more retires the oldest that no decode call is reading (its handle turns invalid, its memory is reused).
+ * the 43 LLRs per payload byte crossing PCIe twice.  A producer always keeps its W80211_LEASES_KEPT newest leases, and older
+ * ones too while it holds at most 64 leases and W80211_LEASE_BYTES of device memory in them (environment, default 4 GiB: a
+ * consumer may lag by whatever the edge between the blocks buffers); beyond that an export retires the oldest lease that no
+ * decode call is reading (its handle turns invalid, its memory is reused).
  * decode_submit() is the non-blocking form of decode_batch(): LLRs from host memory (in->llr must stay valid until
  * collect), device memory, or a lease (in->llr ignored; desc[p].llr_off are the offsets demod reported).  Results arrive
  * at w80211_rx_collect(ctx, slot) in *out exactly as for decode_batch(). */

@@ -378,11 +378,12 @@ def test_llrs_outside_the_stated_domain_never_publish_a_wrong_frame(refgr, rx):
     assert in_domain(got) == in_domain(want)
 
 
-def test_demod_and_decode_as_separate_non_blocking_stages_joined_by_llr_leases():
+def test_demod_and_decode_as_separate_non_blocking_stages_joined_by_llr_leases(monkeypatch):
     """What the two GR blocks do (ABI 7): w80211_demod_submit on one context, the batch's LLRs exported as a lease after
     collect, w80211_decode_submit on ANOTHER context of the same GPU reading that lease -- two batches in flight on each
-    side.  Results equal the fused path's; a producer keeps its W80211_LEASES_KEPT newest leases, older handles turn
-    invalid and decode refuses them; destroying the producer retires the rest."""
+    side.  Results equal the fused path's; with no byte allowance for older leases (W80211_LEASE_BYTES = 0) a producer keeps
+    its W80211_LEASES_KEPT newest, older handles turn invalid and decode refuses them; destroying the producer retires the rest."""
+    monkeypatch.setenv("W80211_LEASE_BYTES", "0")
     dm, dc = host.Receiver(0, nslots=2), host.Receiver(0, nslots=2)
     try:
         batches = [gp.gen_batch(g.F_L, 7, 1, 700, 5, snr_db=30, seed=170), gp.gen_batch(g.F_HT, 7, 1, 1200, 4, snr_db=30, short_gi=True, seed=171),

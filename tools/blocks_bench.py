@@ -57,7 +57,7 @@ def run(npkt=4096, ref_packets=48, modes=("auto", "both", "host"), config="C4", 
             ours.run_chain(warm, blocks=blocks, ring_items=1 << 22, chunk_out=1 << 16)  # contexts, buffers, kernels loaded
             best = None
             reps = []
-            for rep in range(3):
+            for rep in range(5):  # the first ones still grow the three batch sets of each block
                 tm = {}
                 msgs = ours.run_chain(streams, blocks=blocks, ring_items=1 << 22, chunk_out=1 << 16, timing=tm)
                 ok = sum(1 for m in msgs if m[3:-1] in sent)

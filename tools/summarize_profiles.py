@@ -67,7 +67,7 @@ def launch_table():
             g0 = int(grid.strip("()").split(",")[0])
             full = {"viterbi_kernel": npk // 32, "traceback_kernel": npk // 32, "demod_kernel": None}[base]
             if base == "demod_kernel":
-                full = g0 if g0 > 150000 else None  # 113664 packets x 14 work items / 8 per block
+                full = npk * 3 // 8  # 113664 packets x 3 work items (105 symbols in runs of 35) / 8 items per block
             if full is not None and g0 == full and base not in traffic:
                 traffic[base] = {"dram_bytes_per_packet": a[2] / a[0] / npk, "algorithmic_bytes_per_packet": alg[base]}
     json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
@@ -116,5 +116,14 @@ if __name__ == "__main__":
     txt = ncu_report("prof_front.ncu-rep", "ncu --set full --clock-control none --import-source on -k regex:'presiso|cfo_copy|lsig|sync_event|run_edges' -c 6\n"
                      "same command: the front-end kernels (SURVEY 8(f) N3 + N1), first launches of the front-end leg (28416 short packets, 45 M samples)")
     open(os.path.join(P, "%s_ncu_front_end.txt" % tag), "w").write("\n".join(txt) + "\n")
+    txt = ncu_report("prof_demod2.ncu-rep", "ncu --set full --clock-control none --import-source on -k regex:demod -s 2 -c 1\n"
+                     "command: python bench.py --resident-only --config C5 --packets 14208 --steps 2 --warmup 1   (the two-antenna demodulator on\n"
+                     "full-size C5 packets: HT MCS15, 64 symbols, two streams)")
+    for rep, kre in (("prof_round.ncu-rep", "demod"), ("prof_demod2.ncu-rep", "demod"), ("prof_round.ncu-rep", "viterbi")):
+        if os.path.exists(os.path.join(G, rep)):
+            txt += ["", "per opcode (tools/ncu_ops.py %s %s):" % (rep, kre)]
+            txt += subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_ops.py"), os.path.join(G, rep), kre, "14"],
+                                  capture_output=True, text=True).stdout.splitlines()
+    open(os.path.join(P, "%s_ncu_demod2_and_opcodes.txt" % tag), "w").write("\n".join(txt) + "\n")
     print(open(os.path.join(P, "%s_launch_summary.txt" % tag)).read())
     print(open(os.path.join(P, "traffic.json")).read())
