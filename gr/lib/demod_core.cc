@@ -265,8 +265,13 @@ bool demod_core::start_packet(uint64_t abs_offset)
             chan = pmt::c32vector_elements(t.value);
         /* "seq" is only printed by the reference */
     }
+    if (nsamp + 320 <= 0 || nsamp > 0x3fffffff) {
+        /* a tag no signal block writes: the tagged item is passed over (the reference would wait on it for ever) */
+        d_left = 1;
+        d_copy_left = 0;
+        return true;
+    }
     d_left = nsamp + 320; /* demod_impl.cc:92 */
-    if (d_left <= 0) return false; /* the reference never leaves this tag either */
     d_copy_left = std::max(nsamp, 0L);
     pk.nsamp = (int32_t)d_copy_left;
     pk.iq_offset = b.fill;
