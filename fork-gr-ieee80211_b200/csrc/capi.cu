@@ -781,6 +781,8 @@ void run_continuation(w80211_ctx* ctx, Slot& s)
  * upto >= 0: wait for the descriptors of the batches up to and including slot `upto`; -2: of all of them. */
 void progress(w80211_ctx* ctx, int upto)
 {
+    if (ctx->pending.empty()) return;
+    cudaSetDevice(ctx->device); /* the caller may have used a context on another device since (one process, several GPUs) */
     while (!ctx->pending.empty()) {
         const int idx = ctx->pending.front();
         Slot& s = ctx->slots[idx];
