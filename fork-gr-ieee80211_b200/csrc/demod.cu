@@ -182,10 +182,12 @@ __device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, 
 /* dynamic shared memory of one block (the two-antenna variant needs more than the 48 KB static limit) */
 template <bool MIMO>
 struct DemodSmem {
-    double eqr[DEMOD_GROUPS][64];                                  /* per bin: RN(1 / |H|^2) in binary64 */
-    float stage[DEMOD_GROUPS][(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2) + DEMOD_PAD]; /* one symbol's LLRs per group, deinterleaved: the
+    double eqr[MIMO ? 1 : DEMOD_GROUPS][MIMO ? 1 : 64];            /* per bin: RN(1 / |H|^2) in binary64.  Not kept by the two-antenna
+                                                                      variant (its one-stream packets recompute it): at 31.9 KB
+                                                                      per block four blocks leave the SM 32 KB more L1 */
+    alignas(16) float stage[DEMOD_GROUPS][(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2) + DEMOD_PAD]; /* one symbol's LLRs per group, deinterleaved: the
                                                                       source of the bulk store; the pad holds the dump slot */
-    float2 xch[DEMOD_GROUPS][W_FFT_XCH_FLOAT2];                    /* FFT exchange area of the group (the staging row may still be
+    alignas(16) float2 xch[DEMOD_GROUPS][W_FFT_XCH_FLOAT2];                    /* FFT exchange area of the group (the staging row may still be
                                                                       draining when the next symbol's FFT runs) */
     float2 tw[8 * 9];                                              /* W64^(g*k1) at [g*9 + k1] */
 };
@@ -271,7 +273,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MI
         const double hc = hh[k2].x, hd = hh[k2].y;
         const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
         slow_div = slow_div || d_recip_unsafe(denom);
-        eqr[grp][i] = __drcp_rn(denom);
+        if (!MIMO) eqr[grp][i] = __drcp_rn(denom);
     }
     const int z = fmt == W80211_F_L ? 1 : (fmt == W80211_F_HT ? 3 : 4);
     const bool ht2 = two && fmt == W80211_F_HT;
@@ -318,7 +320,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MI
                 asm volatile("" : "+f"(hh[k2].x), "+f"(hh[k2].y));
                 const double hc = hh[k2].x, hd = hh[k2].y;
                 const double denom = __dadd_rn(__dmul_rn(hc, hc), __dmul_rn(hd, hd));
-                e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, eqr[grp][i]);
+                e1[k2] = slow_div ? c_div(c_make(re[k2], im[k2]), hh[k2]) : c_div_known(c_make(re[k2], im[k2]), hh[k2], denom, MIMO ? __drcp_rn(denom) : eqr[MIMO ? 0 : grp][MIMO ? 0 : i]);
             }
         } else {
             /* two streams: H^H y, then the inverse of H^H H (demod2_impl.cc:471-630), every bin and every lane alike -- no
