@@ -105,6 +105,7 @@ struct SigStage {
     PinBuf h_res, h_acc;
     /* detection stage */
     DevBuf det_ac, det_conj, det_sig, det_cnt, det_starts, det_ends, det_tmp, det_ev, det_res;
+    DevBuf str_sig, str_ac, str_conj; /* w80211_detect_stream: samples and presiso streams of the buffer being examined */
     PinBuf h_edges, h_ev, h_dres;
     unsigned int edge_cap = 4096; /* run edges the lists are sized for: one and a half times what the last call found */
 };
@@ -889,7 +890,7 @@ void w80211_destroy(w80211_ctx* ctx)
     {
         SigStage& g = ctx->sig;
         DevBuf* db[] = {&g.iq[0], &g.iq[1], &g.syncs, &g.res, &g.chan_all, &g.acc, &g.out_iq[0], &g.out_iq[1], &g.out_chan,
-                        &g.det_ac, &g.det_conj, &g.det_sig, &g.det_cnt, &g.det_starts, &g.det_ends, &g.det_tmp, &g.det_ev, &g.det_res};
+                        &g.det_ac, &g.det_conj, &g.det_sig, &g.det_cnt, &g.det_starts, &g.det_ends, &g.det_tmp, &g.str_sig, &g.str_ac, &g.str_conj, &g.det_ev, &g.det_res};
         for (DevBuf* b : db)
             if (b->p) cudaFree(b->p);
         if (g.h_res.p) cudaFreeHost(g.h_res.p);
@@ -1327,6 +1328,45 @@ int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_dete
     out->state = next > 0 ? s1 : st0; /* next = 0: nothing was consumed */
     ctx->stats.kernel_launches += 4;
     return W80211_OK;
+}
+
+int w80211_detect_stream(w80211_ctx* ctx, const float* sig, uint64_t nsamples, uint64_t lead, int32_t mem, int32_t final,
+                         const w80211_detect_state* state, w80211_detect_out* out)
+{
+    NvtxRange nvtx_("w80211 detect_stream");
+    if (!ctx) return W80211_E_ARG;
+    if (!out || lead > nsamples || nsamples >= 0xffffffffull || (nsamples > 0 && !sig)) return fail(ctx, W80211_E_ARG, "bad detect_stream arguments");
+    CK(cudaSetDevice(ctx->device));
+    SigStage& g = ctx->sig;
+    if (!g.stream) {
+        CK(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+        for (auto& e : g.ev) CK(cudaEventCreate(&e));
+    }
+    cudaStream_t st = g.stream;
+    const float2* d_sg = (const float2*)sig;
+    if (nsamples > 0) {
+        if (mem != W80211_MEM_DEVICE) {
+            RS(dev_reserve(ctx, g.str_sig, (size_t)nsamples * 8 + 64));
+            CK(cudaMemcpyAsync(g.str_sig.p, sig, (size_t)nsamples * 8, cudaMemcpyHostToDevice, st));
+            d_sg = (const float2*)g.str_sig.p;
+        }
+        RS(dev_reserve(ctx, g.str_ac, (size_t)nsamples * 4 + 64));
+        RS(dev_reserve(ctx, g.str_conj, (size_t)nsamples * 8 + 64));
+        w_launch_presiso(st, d_sg, nsamples, (float*)g.str_ac.p, (float2*)g.str_conj.p);
+        CK(cudaGetLastError());
+        ctx->stats.kernel_launches += 1;
+    }
+    /* the detection proper, on the same stream, from the device-resident streams past the history */
+    w80211_detect_in din;
+    memset(&din, 0, sizeof(din));
+    din.mem = W80211_MEM_DEVICE;
+    din.final = final;
+    din.nsamples = nsamples - lead;
+    din.preac = (const float*)g.str_ac.p + lead;
+    din.preconj = (const float*)((const float2*)g.str_conj.p + lead);
+    din.sig = (const float*)(d_sg + lead);
+    din.state = state;
+    return w80211_detect_batch(ctx, &din, out);
 }
 
 int w80211_signal_batch(w80211_ctx* ctx, const w80211_signal_in* in, w80211_signal_out* out)

@@ -21,7 +21,7 @@ SYMBOLS = [
     "w80211_timing_get", "w80211_stream", "w80211_demod_batch", "w80211_decode_batch", "w80211_rx_submit",
     "w80211_rx_collect", "w80211_rx_batch", "w80211_host_alloc", "w80211_host_free", "w80211_signal_batch",
     "w80211_detect_batch", "w80211_presiso_batch", "w80211_viterbi_noalloc", "w80211_rx_poll", "w80211_demod_submit",
-    "w80211_decode_submit", "w80211_llr_export", "w80211_llr_query", "w80211_lease_consumers",
+    "w80211_decode_submit", "w80211_llr_export", "w80211_llr_query", "w80211_lease_consumers", "w80211_detect_stream",
 ]
 
 
@@ -155,6 +155,7 @@ def load():
         L.w80211_llr_export.argtypes = [vp, C.c_int, C.POINTER(C.c_uint64)]
         L.w80211_llr_query.argtypes = [C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_uint64)]
         L.w80211_lease_consumers.argtypes = [C.c_int]
+        L.w80211_detect_stream.argtypes = [vp, vp, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(DetectState), C.POINTER(DetectOut)]
         _lib = L
     return _lib
 
@@ -473,6 +474,20 @@ class Receiver:
         sy = np.zeros(cap, SYNC_DTYPE)
         do.sync_capacity, do.syncs = cap, sy.ctypes.data
         self._check(self.L.w80211_detect_batch(self.h, C.byref(di), C.byref(do)))
+        st = DetectState()
+        C.memmove(C.byref(st), C.byref(do.state), C.sizeof(DetectState))
+        return {"syncs": sy[:do.nsync].copy(), "next": int(do.next), "state": st, "n_trigger": int(do.n_trigger)}
+
+    def detect_stream(self, sig, lead=0, state=None, final=True):
+        """samples (the first `lead` are history) -> sync flags, presiso streams kept on the GPU (w80211_detect_stream)."""
+        sig = np.ascontiguousarray(sig, np.complex64)
+        n = len(sig)
+        do = DetectOut()
+        cap = n // 100 + 16
+        sy = np.zeros(cap, SYNC_DTYPE)
+        do.sync_capacity, do.syncs = cap, sy.ctypes.data
+        self._check(self.L.w80211_detect_stream(self.h, sig.ctypes.data, n, int(lead), MEM_HOST, int(bool(final)),
+                                                C.pointer(state) if state is not None else None, C.byref(do)))
         st = DetectState()
         C.memmove(C.byref(st), C.byref(do.state), C.sizeof(DetectState))
         return {"syncs": sy[:do.nsync].copy(), "next": int(do.next), "state": st, "n_trigger": int(do.n_trigger)}

@@ -9,6 +9,7 @@
 #include <pybind11/pybind11.h>
 
 #include <gnuradio/ieee80211/decode.h>
+#include <gnuradio/ieee80211/detect.h>
 #include <gnuradio/ieee80211/demod.h>
 #include <gnuradio/ieee80211/demod2.h>
 #include <gnuradio/ieee80211/signal.h>
@@ -49,4 +50,13 @@ void bind_decode(py::module& m)
     using blk = ::gr::ieee80211::decode;
     py::class_<blk, gr::block, gr::basic_block, std::shared_ptr<blk>>(m, "decode", "802.11 BCC decoder (B200)")
         .def(py::init(&blk::make), py::arg("ifdebug"));
+}
+
+/* new block (no counterpart in the reference's bindings): add `void bind_detect(py::module&);` and a call to it in
+ * python_bindings.cc when gr/lib/detect_impl.cc is built in */
+void bind_detect(py::module& m)
+{
+    using blk = ::gr::ieee80211::detect;
+    py::class_<blk, gr::block, gr::basic_block, std::shared_ptr<blk>>(m, "detect", "802.11 packet detection: presiso + trigger + sync in one block (B200)")
+        .def(py::init(&blk::make));
 }

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define W80211_ABI_VERSION 7
+#define W80211_ABI_VERSION 8
 
 /* packet formats: the reference's C8P_F_L / C8P_F_HT / C8P_F_VHT (lib/cloud80211phy.h:35-37) */
 #define W80211_F_L 0
@@ -289,6 +289,14 @@ int w80211_presiso_batch(w80211_ctx* ctx, const float* sig, uint64_t nsamples, i
  * sequential binary32 running sums.  Flag positions and rssi are exact; rad and snr go through atan2f / cosf / sinf /
  * log10 and agree with a host libm to a few ulp.  Synchronous, on the signal stage's stream. */
 int w80211_detect_batch(w80211_ctx* ctx, const w80211_detect_in* in, w80211_detect_out* out);
+
+/* Received samples -> sync flags in one call: w80211_presiso_batch + w80211_detect_batch with the two presiso streams kept
+ * in HBM (what presiso.grc + trigger + sync do between the sample source and signal; this is what gr/lib's `detect` block
+ * calls).  sig holds `lead` samples of history (at most what the previous call left unexamined plus 79 or more before it; 0
+ * at the start of a stream, where earlier samples count as zero) followed by the nsamples - lead samples to examine;
+ * positions in *out (syncs[].pos, next) count from sig + lead.  state / final / out as for w80211_detect_batch. */
+int w80211_detect_stream(w80211_ctx* ctx, const float* sig, uint64_t nsamples, uint64_t lead, int32_t mem, int32_t final,
+                         const w80211_detect_state* state, w80211_detect_out* out);
 
 /* Raw samples + sync flags -> packets in demod's input format: what signal / signal2 do between sync and demod
  * (lib/signal_impl.cc:62-212, lib/signal2_impl.cc:62-222).  Every flag's L-SIG is demodulated and decoded in

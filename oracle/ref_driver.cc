@@ -24,6 +24,9 @@
 #include <gnuradio/ieee80211/demod2.h>
 #include <gnuradio/ieee80211/signal.h>
 #include <gnuradio/ieee80211/signal2.h>
+#ifdef W80211_DRIVER_OURS
+#include <gnuradio/ieee80211/detect.h>
+#endif
 #ifndef W80211_DRIVER_OURS
 #include <gnuradio/ieee80211/sync.h>
 #include <gnuradio/ieee80211/trigger.h>
@@ -129,6 +132,10 @@ ref_block* ref_block_new(const char* kind, int a0, int a1)
             b->blk = gr::ieee80211::sync::make();
         b->honor_forecast = true;
     }
+#endif
+#ifdef W80211_DRIVER_OURS
+    else if (k == "detect")
+        b->blk = gr::ieee80211::detect::make();
 #endif
     else if (k == "demod")
         b->blk = gr::ieee80211::demod::make(a0, a1);

@@ -235,6 +235,15 @@ def run_sync(trigger_stream, preconj, sig, chunk_in=0, chunk_out=8192):
     return out
 
 
+def run_detect(sig, chunk_in=0, chunk_out=8192):
+    """received samples -> the sync flag stream with tags rad / snr / rssi, through this repo's `detect` block (the harness
+    build of gr/lib only: the reference has presiso + trigger + sync in its place)."""
+    blk = Block("detect")
+    out = Stream(itemsize=1)
+    blk.run([Stream(np.asarray(sig, np.complex64))], out, chunk_in, chunk_out)
+    return out
+
+
 def run_demod(sig_streams, mupos=0, mugid=2, chunk_in=0, chunk_out=8192):
     """signal-format stream(s) -> LLR stream with demod's tags."""
     blk = Block("demod", mupos, mugid) if len(sig_streams) == 1 else Block("demod2")

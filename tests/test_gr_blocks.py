@@ -253,3 +253,35 @@ def test_signal_block_stream_matches_the_reference(refgr, ours, nant, chunks):
     ref_msgs = refgr.run_decode(refgr.run_demod(ref_out))
     our_msgs = ours.run_decode(ours.run_demod(our_out))
     assert our_msgs == ref_msgs and len(ref_msgs) >= len(pos) - 1
+
+
+# ------------------------------------------------------------------ detect
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunks", [(0, 8192, 1 << 20), (1000, 700, 1 << 20), (4099, 8192, 2048), (0, 8192, 700)])
+def test_detect_block_flags_are_the_reference_chain_s(refgr, ours, monkeypatch, chunks):
+    """This repo's `detect` block (one block for presiso + trigger + sync) against the reference's trigger -> sync blocks fed
+    GNU Radio's presiso streams (oracle/port/presiso_port.c, running sums carried as in 3.10): a flag at the same items, with
+    rad / snr / rssi to the tolerance of the presiso contract, for scheduler windows and GPU chunks of several sizes (chunks
+    that cut runs, countdowns and sync windows); then the rest of the chain on each side's flags publishes the same frames."""
+    from oracle import port
+    monkeypatch.setenv("W80211_DETECT_CHUNK", str(chunks[2]))
+    bs = [gp.gen_batch(g.F_HT, 5, 1, 300, 3, snr_db=25, seed=950), gp.gen_batch(g.F_L, 3, 1, 100, 3, snr_db=25, seed=951),
+          gp.gen_batch(g.F_VHT, 4, 1, 500, 3, snr_db=25, seed=952)]
+    raw, pos, rad = build_stream(bs, [0.01, -0.02, 0.004], gap=600, noise=0.03, seed=95)
+    x = raw[0]
+    ac, cj = port.presiso(x, 0)
+    ref = refgr.run_sync(refgr.run_trigger(ac), cj, x)
+    mine = ours.run_detect(x, chunk_in=chunks[0], chunk_out=chunks[1])
+    rt, mt = ref.tags(), mine.tags()
+    assert [o for o, _ in mt] == [o for o, _ in rt] and len(rt) == len(pos)
+    md, rd = mine.data(), ref.data()
+    assert len(md) <= len(x) and np.array_equal(np.flatnonzero(md), np.flatnonzero(rd[: len(md)]))
+    for (_, a), (_, b) in zip(mt, rt):
+        assert set(a) == set(b) == {"rad", "snr", "rssi"}
+        assert abs(a["rad"] - b["rad"]) <= 1e-4 and abs(a["snr"] - b["snr"]) <= 1e-2 * max(1.0, abs(b["snr"]))
+        assert abs(a["rssi"] - b["rssi"]) <= 1e-4 * abs(b["rssi"])
+    ref_msgs = refgr.run_decode(refgr.run_demod(refgr.run_signal(raw, [o for o, _ in rt], rad=[t["rad"] for _, t in rt])))
+    sig = ours.Block("signal")
+    out = ours.Stream(itemsize=8)
+    sig.run([mine, ours.Stream(x[: len(md)])], [out])
+    assert ours.run_decode(ours.run_demod([out])) == ref_msgs and len(ref_msgs) == len(pos)

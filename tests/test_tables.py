@@ -104,7 +104,7 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(host.SYMBOLS), declared ^ set(host.SYMBOLS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.w80211_abi_version() == 7
+    assert L.w80211_abi_version() == 8
 
 
 def test_struct_layouts_match():
