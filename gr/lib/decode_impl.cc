@@ -477,6 +477,17 @@ int decode_impl::general_work(int /*noutput_items*/,
         finish_front(true);
         take_free_set();
     }
+    if (d_trace && consumed == 0 && navail > 0) {
+        static int said = 0;
+        if (said++ < 20) {
+            std::vector<gr::tag_t> tg;
+            get_tags_in_range(tg, 0, nitems_read(0), nitems_read(0) + 1);
+            std::fprintf(stderr, "ieee80211 decode trace: nothing consumed of %d items at %llu: d_left %ld d_cur %d queue %zu partial_in %d states %d %d %d "
+                                 "published %d tags-at-item %zu ncomplete %d\n",
+                         navail, (unsigned long long)nitems_read(0), d_left, d_cur, d_queue.size(), d_partial_in, (int)d_sets[0].state,
+                         (int)d_sets[1].state, (int)d_sets[2].state, (int)published, tg.size(), d_cur >= 0 ? d_sets[d_cur].ncomplete : -1);
+        }
+    }
     consume_each(consumed);
     return 0;
 }

@@ -15,7 +15,14 @@
  * Test infrastructure only. */
 #pragma once
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstdio>
 #include <cstring>
+#include <exception>
+#include <mutex>
+#include <thread>
 #include <gnuradio/block.h>
 
 namespace gr {
@@ -214,6 +221,192 @@ inline long mock_run_chain(block& up,
         if (idle >= MOCK_IDLE_STOP) break;
     }
     return calls;
+}
+
+/* The same two blocks, each on a thread of its own like under GNU Radio's thread-per-block scheduler.  The edge is the same
+ * linear buffer of `ring_items` items: the upstream thread writes behind the last written item while the downstream thread
+ * reads its window; when the tail is reached the unread items are moved to the front, which the upstream thread does while
+ * holding the lock the downstream thread holds during its general_work() (windows stay contiguous, as windows of GNU Radio's
+ * double-mapped buffers are).  Positions and the edge's tags are guarded by one mutex; a thread that made no progress waits
+ * for the other on a condition variable (1 ms at most).  The upstream thread ends after it has seen all its input and made no
+ * progress MOCK_IDLE_STOP times in a row, the downstream one after that and the same.  Returns the general_work calls of both. */
+inline long mock_run_chain_threads(block& up, block& down, const std::vector<const mock_stream*>& ins, long ring_items, long chunk_in,
+                                   long chunk_out)
+{
+    const size_t nin = ins.size();
+    mock_stream mid(up.mock_outsig ? up.mock_outsig->sizeof_stream_item(0) : 4);
+    mid.tags_sorted = true;
+    std::mutex mu, window_mu;
+    std::condition_variable cv;
+    mid.lock = &mu;
+    if (ring_items < 4 * 4096) ring_items = 4 * 4096;
+    if (chunk_in <= 0) chunk_in = 1L << 40;
+    if (chunk_out <= 0) chunk_out = 8192;
+    if (chunk_out > ring_items / 2) chunk_out = ring_items / 2;
+    mid.data.resize((size_t)ring_items * mid.itemsize);
+    up.mock_in = ins;
+    up.mock_out.assign(1, &mid);
+    up.mock_nread.assign(nin, 0);
+    up.mock_nwritten.assign(1, 0);
+    up.mock_consumed.assign(nin, 0);
+    down.mock_in.assign(1, &mid);
+    down.mock_out.clear();
+    down.mock_nread.assign(1, 0);
+    down.mock_nwritten.clear();
+    down.mock_consumed.assign(1, 0);
+    uint64_t w = 0, r = 0, base = 0; /* absolute items written / read / at data[0]; guarded by mu */
+    bool up_done = false;
+    std::atomic<long> calls(0);
+    /* a flowgraph that stops moving is a bug to report, not to wait out: no progress on either side for MOCK_STALL_S seconds
+     * ends the run with a line on stderr */
+    const double MOCK_STALL_S = 20.0;
+    auto now_s = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    std::atomic<double> last_progress(now_s());
+    std::atomic<bool> stalled(false);
+
+    std::exception_ptr up_error;
+    std::thread producer([&] {
+      try {
+        std::vector<uint64_t> pos(nin, 0);
+        long win_in = chunk_in;
+        int idle = 0;
+        for (;;) {
+            long room;
+            uint64_t at;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                if ((long)(w - base) + chunk_out > ring_items && r > base) {
+                    lk.unlock();
+                    std::lock_guard<std::mutex> wl(window_mu); /* the reader is between two calls */
+                    lk.lock();
+                    const uint64_t keep = w - r;
+                    if (keep) std::memmove(mid.data.data(), mid.data.data() + (size_t)(r - base) * mid.itemsize, (size_t)keep * mid.itemsize);
+                    base = r;
+                }
+                room = std::min<long>(chunk_out, ring_items - (long)(w - base));
+                at = w - base;
+            }
+            bool progress = false, sees_all = true;
+            if (room > 0) {
+                gr_vector_int ninput(nin);
+                gr_vector_const_void_star in_ptrs(nin);
+                gr_vector_void_star out_ptrs(1);
+                for (size_t i = 0; i < nin; i++) {
+                    const uint64_t rem = ins[i]->nitems() - pos[i];
+                    const uint64_t n = std::min<uint64_t>(rem, (uint64_t)win_in);
+                    if (n < rem) sees_all = false;
+                    ninput[i] = (int)std::min<uint64_t>(n, 0x7fffffffu);
+                    in_ptrs[i] = ins[i]->data.data() + pos[i] * ins[i]->itemsize;
+                }
+                out_ptrs[0] = mid.data.data() + (size_t)at * mid.itemsize; /* only this thread moves w and base */
+                std::fill(up.mock_consumed.begin(), up.mock_consumed.end(), 0);
+                const int produced = up.general_work((int)room, ninput, in_ptrs, out_ptrs);
+                calls++;
+                for (size_t i = 0; i < nin; i++)
+                    if (up.mock_consumed[i] > 0) {
+                        pos[i] += up.mock_consumed[i];
+                        up.mock_nread[i] += up.mock_consumed[i];
+                        progress = true;
+                    }
+                if (produced > 0) {
+                    std::unique_lock<std::mutex> lk(mu);
+                    w += (uint64_t)produced;
+                    up.mock_nwritten[0] = w;
+                    progress = true;
+                    cv.notify_all();
+                }
+            }
+            if (progress) {
+                idle = 0;
+                win_in = chunk_in;
+                last_progress = now_s();
+                continue;
+            }
+            idle++;
+            if (idle >= MOCK_IDLE_GROW && !sees_all && room > 0) {
+                win_in *= 2;
+                idle = 0;
+                continue;
+            }
+            if (idle >= MOCK_IDLE_STOP && sees_all && room > 0) break;
+            if (stalled || now_s() - last_progress > MOCK_STALL_S) {
+                std::unique_lock<std::mutex> lk(mu);
+                if (!stalled)
+                    fprintf(stderr, "mock_run_chain_threads: STALLED (upstream): w %llu r %llu base %llu room %ld idle %d sees_all %d\n",
+                            (unsigned long long)w, (unsigned long long)r, (unsigned long long)base, room, idle, (int)sees_all);
+                stalled = true;
+                break;
+            }
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait_for(lk, std::chrono::milliseconds(1));
+        }
+      } catch (...) {
+        up_error = std::current_exception(); /* rethrown by the calling thread after the join */
+      }
+        std::unique_lock<std::mutex> lk(mu);
+        up_done = true;
+        cv.notify_all();
+    });
+
+    int idle = 0;
+    std::exception_ptr down_error;
+    try {
+    for (;;) {
+        bool done, moved = false;
+        {
+            std::lock_guard<std::mutex> wl(window_mu); /* the window must not move while the block reads it */
+            uint64_t avail, at;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                avail = w - r;
+                at = r - base;
+                done = up_done;
+            }
+            gr_vector_int ninput(1, (int)std::min<uint64_t>(avail, 0x7fffffffu));
+            gr_vector_const_void_star in_ptrs(1, mid.data.data() + (size_t)at * mid.itemsize);
+            gr_vector_void_star out_ptrs;
+            down.mock_consumed[0] = 0;
+            down.general_work(0, ninput, in_ptrs, out_ptrs);
+            calls++;
+            if (down.mock_consumed[0] > 0) {
+                std::unique_lock<std::mutex> lk(mu);
+                r += (uint64_t)down.mock_consumed[0];
+                down.mock_nread[0] = r;
+                size_t k = 0;
+                while (k < mid.tags.size() && mid.tags[k].offset < r) k++;
+                if (k > 4096 || k == mid.tags.size()) mid.tags.erase(mid.tags.begin(), mid.tags.begin() + (long)k);
+                cv.notify_all();
+                moved = true;
+            }
+        }
+        if (moved) {
+            idle = 0;
+            last_progress = now_s();
+            continue;
+        }
+        if (done && ++idle >= MOCK_IDLE_STOP) break;
+        if (stalled || now_s() - last_progress > MOCK_STALL_S) {
+            std::unique_lock<std::mutex> lk(mu);
+            if (!stalled)
+                fprintf(stderr, "mock_run_chain_threads: STALLED (downstream): w %llu r %llu base %llu done %d idle %d\n", (unsigned long long)w,
+                        (unsigned long long)r, (unsigned long long)base, (int)done, idle);
+            stalled = true;
+            cv.notify_all();
+            break;
+        }
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait_for(lk, std::chrono::milliseconds(1));
+    }
+    } catch (...) {
+        down_error = std::current_exception();
+        stalled = true; /* stops the upstream thread */
+        cv.notify_all();
+    }
+    producer.join();
+    mid.lock = nullptr;
+    if (down_error) std::rethrow_exception(down_error);
+    if (up_error) std::rethrow_exception(up_error);
+    return stalled ? -2 : calls.load();
 }
 
 } // namespace gr

@@ -9,6 +9,7 @@
 #include <iostream>
 #include <cstdint>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -24,8 +25,9 @@ struct mock_stream {
     std::vector<uint8_t> data;
     std::vector<tag_t> tags;
     bool tags_sorted; /* tags are in ascending offset order: get_tags_in_range() may use a binary search */
-    mock_stream() : itemsize(1), tags_sorted(false) {}
-    explicit mock_stream(int isz) : itemsize(isz), tags_sorted(false) {}
+    std::mutex* lock; /* set while two scheduler threads share the stream (mock_run_chain_threads): guards `tags` */
+    mock_stream() : itemsize(1), tags_sorted(false), lock(nullptr) {}
+    explicit mock_stream(int isz) : itemsize(isz), tags_sorted(false), lock(nullptr) {}
     uint64_t nitems() const { return itemsize ? data.size() / itemsize : 0; }
 };
 
@@ -90,6 +92,8 @@ public:
     {
         v.clear();
         const mock_stream* s = mock_in.at(which_input);
+        std::unique_lock<std::mutex> guard;
+        if (s->lock) guard = std::unique_lock<std::mutex>(*s->lock);
         if (s->tags_sorted) {
             auto it = std::lower_bound(s->tags.begin(), s->tags.end(), abs_start, [](const tag_t& t, uint64_t o) { return t.offset < o; });
             for (; it != s->tags.end() && it->offset < abs_end; ++it) v.push_back(*it);
@@ -109,7 +113,10 @@ public:
         t.key = key;
         t.value = value;
         t.srcid = srcid;
-        mock_out.at(which_output)->tags.push_back(t);
+        mock_stream* o = mock_out.at(which_output);
+        std::unique_lock<std::mutex> guard;
+        if (o->lock) guard = std::unique_lock<std::mutex>(*o->lock);
+        o->tags.push_back(t);
     }
     pmt::pmt_t alias_pmt() const { return pmt::mp(mock_name); }
     void set_tag_propagation_policy(tag_propagation_policy_t p) { mock_tpp = p; }

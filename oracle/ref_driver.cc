@@ -173,14 +173,15 @@ long ref_block_run(ref_block* b, mock_stream** ins, int nin, mock_stream** outs,
     b->blk->mock_msgs.clear();
     return calls;
 }
-/* demod -> decode joined by a bounded edge, run in turn by one thread (mock_run_chain): the streaming form both the
- * block-path benchmark and the chain tests use.  Messages land in `down`. */
-long ref_chain_run(ref_block* up, ref_block* down, mock_stream** ins, int nin, long ring_items, long chunk_in, long chunk_out)
+/* demod -> decode joined by a bounded edge, run in turn by one thread (mock_run_chain) or each on a thread of its own
+ * (mock_run_chain_threads): the streaming forms the block-path benchmark and the chain tests use.  Messages land in `down`. */
+long ref_chain_run(ref_block* up, ref_block* down, mock_stream** ins, int nin, long ring_items, long chunk_in, long chunk_out, int threads)
 {
     std::vector<const mock_stream*> vin(ins, ins + nin);
     long calls;
     try {
-        calls = gr::mock_run_chain(*up->blk, *down->blk, vin, ring_items, chunk_in, chunk_out);
+        calls = threads ? gr::mock_run_chain_threads(*up->blk, *down->blk, vin, ring_items, chunk_in, chunk_out)
+                        : gr::mock_run_chain(*up->blk, *down->blk, vin, ring_items, chunk_in, chunk_out);
     } catch (const std::exception& e) {
         fprintf(stderr, "ref_chain_run: exception: %s\n", e.what());
         return -1;

@@ -48,7 +48,7 @@ def lib():
         L.ref_stream_add_tag_c32.argtypes = [vp, cl, C.c_char_p, vp, ci]
         L.ref_stream_sort_tags.argtypes = [vp]
         L.ref_chain_run.restype = cl
-        L.ref_chain_run.argtypes = [vp, vp, C.POINTER(vp), ci, cl, cl, cl]
+        L.ref_chain_run.argtypes = [vp, vp, C.POINTER(vp), ci, cl, cl, cl, ci]
         L.ref_stream_ntags.argtypes = [vp]
         L.ref_stream_tag_offset.restype = cl
         L.ref_stream_tag_offset.argtypes = [vp, ci]
@@ -259,9 +259,11 @@ def run_decode(llr_stream, debug=False, chunk_in=0, chunk_out=8192):
     return blk.messages()
 
 
-def run_chain(sig_streams, mupos=0, mugid=2, debug=False, ring_items=1 << 20, chunk_in=0, chunk_out=8192, blocks=None, timing=None):
+def run_chain(sig_streams, mupos=0, mugid=2, debug=False, ring_items=1 << 20, chunk_in=0, chunk_out=8192, blocks=None, timing=None,
+              threads=False):
     """demod / demod2 -> decode joined by a bounded edge and run in turn by one thread (mock_run_chain), the way a
-    flowgraph streams: signal-format stream(s) -> list of published blobs.  blocks: an (upstream, downstream) pair to
+    flowgraph streams: signal-format stream(s) -> list of published blobs.  threads: each block on a thread of its own
+    (mock_run_chain_threads), like under GNU Radio's thread-per-block scheduler.  blocks: an (upstream, downstream) pair to
     reuse (both must stand at a packet boundary); timing: a dict that receives the seconds spent inside the two blocks'
     run ("chain_s") and the general_work calls made."""
     import time
@@ -271,7 +273,7 @@ def run_chain(sig_streams, mupos=0, mugid=2, debug=False, ring_items=1 << 20, ch
     up, down = blocks
     arr = (C.c_void_p * len(sig_streams))(*[s.h for s in sig_streams])
     t0 = time.perf_counter()
-    r = L.ref_chain_run(up.h, down.h, arr, len(sig_streams), ring_items, chunk_in, chunk_out)
+    r = L.ref_chain_run(up.h, down.h, arr, len(sig_streams), ring_items, chunk_in, chunk_out, 1 if threads else 0)
     if timing is not None:
         timing["chain_s"] = time.perf_counter() - t0
         timing["calls"] = int(r)

@@ -118,6 +118,8 @@ def test_chain_runner_equals_block_by_block_on_the_reference(refgr):
     assert len(want) == 6
     for ring, cin, cout in [(1 << 20, 0, 8192), (16384, 1500, 1024), (16384, 333, 4096)]:
         assert refgr.run_chain(refgr.make_sig_stream(pk), ring_items=ring, chunk_in=cin, chunk_out=cout) == want
+        # and with each block on a thread of its own (mock_run_chain_threads)
+        assert refgr.run_chain(refgr.make_sig_stream(pk), ring_items=ring, chunk_in=cin, chunk_out=cout, threads=True) == want
 
 
 @pytest.mark.gpu
@@ -137,6 +139,10 @@ def test_streaming_chain_in_every_handoff_mode(refgr, ours, monkeypatch, mode, b
     for ring, cin, cout in [(1 << 20, 0, 8192), (20000, 3000, 2048)]:
         got = ours.run_chain(ours.make_sig_stream(pk, nant=nant), ring_items=ring, chunk_in=cin, chunk_out=cout)
         assert got == want, (ring, len(got), len(want))
+        # each block on a thread of its own, as under GNU Radio's scheduler: two contexts driven from two threads, the lease
+        # table shared between them
+        got = ours.run_chain(ours.make_sig_stream(pk, nant=nant), ring_items=ring, chunk_in=cin, chunk_out=cout, threads=True)
+        assert got == want, ("threads", ring, len(got), len(want))
 
 
 @pytest.mark.gpu
