@@ -211,6 +211,11 @@ def test_blocks_without_a_gpu_drop_packets_and_say_so(refgr, capfd):
     out = ours.run_demod(s)
     assert out.data().size == 0 and out.tags() == []
     assert "no usable CUDA device" in capfd.readouterr().err
+    # the detect block passes its samples unflagged: one zero byte per sample, no tags
+    x = (np.random.default_rng(0).standard_normal(5000) + 0j).astype(np.complex64)
+    flags = ours.run_detect(x, chunk_in=1500)
+    assert flags.data().size == 5000 and not flags.data().any() and flags.tags() == []
+    assert "no usable CUDA device" in capfd.readouterr().err
 
 
 # ------------------------------------------------------------------ signal / signal2
