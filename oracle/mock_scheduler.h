@@ -263,6 +263,16 @@ inline long mock_run_chain_threads(block& up, block& down, const std::vector<con
     auto now_s = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     std::atomic<double> last_progress(now_s());
     std::atomic<bool> stalled(false);
+    /* a thread notifies only when the other one sleeps: a wake-up per call would cost more than the blocks' work */
+    std::atomic<int> sleepers(0);
+    auto nap = [&](std::unique_lock<std::mutex>& lk) {
+        sleepers++;
+        cv.wait_for(lk, std::chrono::milliseconds(1));
+        sleepers--;
+    };
+    auto wake = [&] {
+        if (sleepers.load() > 0) cv.notify_all();
+    };
 
     std::exception_ptr up_error;
     std::thread producer([&] {
@@ -313,7 +323,7 @@ inline long mock_run_chain_threads(block& up, block& down, const std::vector<con
                     w += (uint64_t)produced;
                     up.mock_nwritten[0] = w;
                     progress = true;
-                    cv.notify_all();
+                    wake();
                 }
             }
             if (progress) {
@@ -338,7 +348,7 @@ inline long mock_run_chain_threads(block& up, block& down, const std::vector<con
                 break;
             }
             std::unique_lock<std::mutex> lk(mu);
-            cv.wait_for(lk, std::chrono::milliseconds(1));
+            nap(lk);
         }
       } catch (...) {
         up_error = std::current_exception(); /* rethrown by the calling thread after the join */
@@ -375,7 +385,7 @@ inline long mock_run_chain_threads(block& up, block& down, const std::vector<con
                 size_t k = 0;
                 while (k < mid.tags.size() && mid.tags[k].offset < r) k++;
                 if (k > 4096 || k == mid.tags.size()) mid.tags.erase(mid.tags.begin(), mid.tags.begin() + (long)k);
-                cv.notify_all();
+                wake();
                 moved = true;
             }
         }
@@ -395,7 +405,7 @@ inline long mock_run_chain_threads(block& up, block& down, const std::vector<con
             break;
         }
         std::unique_lock<std::mutex> lk(mu);
-        cv.wait_for(lk, std::chrono::milliseconds(1));
+        nap(lk);
     }
     } catch (...) {
         down_error = std::current_exception();
