@@ -228,7 +228,7 @@ inline long mock_run_chain(block& up,
  * reads its window; when the tail is reached the unread items are moved to the front, which the upstream thread does while
  * holding the lock the downstream thread holds during its general_work() (windows stay contiguous, as windows of GNU Radio's
  * double-mapped buffers are).  Positions and the edge's tags are guarded by one mutex; a thread that made no progress waits
- * for the other on a condition variable (1 ms at most).  The upstream thread ends after it has seen all its input and made no
+ * for the other on a condition variable (0.1 ms at most).  The upstream thread ends after it has seen all its input and made no
  * progress MOCK_IDLE_STOP times in a row, the downstream one after that and the same.  Returns the general_work calls of both. */
 inline long mock_run_chain_threads(block& up, block& down, const std::vector<const mock_stream*>& ins, long ring_items, long chunk_in,
                                    long chunk_out)
@@ -267,7 +267,7 @@ inline long mock_run_chain_threads(block& up, block& down, const std::vector<con
     std::atomic<int> sleepers(0);
     auto nap = [&](std::unique_lock<std::mutex>& lk) {
         sleepers++;
-        cv.wait_for(lk, std::chrono::milliseconds(1));
+        cv.wait_for(lk, std::chrono::microseconds(100)); /* short: the end of a run is 2 x MOCK_IDLE_STOP of these */
         sleepers--;
     };
     auto wake = [&] {
