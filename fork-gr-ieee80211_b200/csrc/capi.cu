@@ -18,6 +18,12 @@
  * the header stage, and the second half of the batch is enqueued by the next API call that finds the descriptors on the
  * host (progress()).  With several slots in flight a batch's demod kernel waits for the previous batch's traceback and
  * post kernels, so the slots alternate and one slot's host work hides behind the other's Viterbi kernel.
+ *
+ * The two halves are also entry points of their own (what the GNU Radio blocks call): demod_submit() is the first half plus
+ * the demod kernel, decode_submit() everything from the Viterbi kernel on, fed from host memory, device memory or an LLR
+ * lease -- the LLR buffer of a collected demod batch, detached from its slot (llr_export) and entered in a process-wide table
+ * (g_leases, one mutex) so that another context on the same GPU, the decode block's, reads it in place.  Retired leases hand
+ * their buffers back to the producer's free list; nothing on that path calls cudaFree.
  */
 #include <algorithm>
 #include <chrono>
