@@ -27,7 +27,10 @@ struct PostSmem {
     uint32_t x2n[32]; /* x^(2^k) mod P, reflected */
     uint32_t dw[POST_WARPS][POST_MAXW];
     uint32_t seq[POST_WARPS][8];
+    const uint32_t* src[POST_WARPS]; /* word 0 of each packet of the block in the traceback's output */
+    int T[POST_WARPS];
 };
+static_assert(POST_MAXW % 32 == 4 && (POST_WARPS & (POST_WARPS - 1)) == 0 && POST_WARPS <= 32, "transposing store: row stride 4 mod 32 banks");
 
 /* a(x) * b(x) mod P, reflected bit order (bit 31 = x^0) */
 __device__ __forceinline__ uint32_t gf_mul(uint32_t a, uint32_t b)
@@ -117,46 +120,62 @@ __global__ void __launch_bounds__(POST_WARPS * 32) post_kernel(const W80211Table
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     for (int i = tid; i < 1024; i += blockDim.x) (&S.crc_tab[0][0])[i] = __ldg(&tab->crc_tab[0][0] + i);
     if (tid < 32) S.x2n[tid] = __ldg(&tab->crc_x2n[tid]);
-    __syncthreads();
     const int q = blockIdx.x * POST_WARPS + wid;
-    if (q >= ndec) return;
-    const int pkt = dec_list[q];
-    const int slot = pkt_slot[pkt];
-    const int4 G = grp[slot >> 5];
+    const bool valid = q < ndec;
+    const int pkt = valid ? dec_list[q] : 0;
     const w80211_desc d = desc[pkt];
     const int T = d.trellis;
-    const int nw = (T + 31) >> 5;
-    const uint32_t* src = bits + (size_t)G.z * 32 + (slot & 31);
-    uint32_t* dw = S.dw[wid];
-
-    /* scrambler state from the first 7 bits (decode_impl.cc:308-314), then 160 sequence bits */
-    uint32_t w0 = __ldg(src);
-    {
-        /* the 160 sequence bits of this state come from the host-made table (tables.cc), six words per warp */
+    if (valid) {
+        const int slot = pkt_slot[pkt];
+        const int4 G = grp[slot >> 5];
+        const uint32_t* src = bits + (size_t)G.z * 32 + (slot & 31);
+        /* scrambler state from the first 7 bits (decode_impl.cc:308-314); the 160 sequence bits of this state come from the
+         * host-made table (tables.cc), six words per packet */
+        const uint32_t w0 = __ldg(src);
         int state = 0;
         for (int i = 0; i < 7; i++)
             if ((w0 >> i) & 1u) state |= 1 << (6 - i);
         if (lane < 6) S.seq[wid][lane] = __ldg(&tab->scr_seq[state][lane]);
-    }
-    __syncwarp();
-    const uint32_t* seq = S.seq[wid];
-    for (int j = lane; j < nw + 1; j += 32) {
-        uint32_t v = 0;
-        if (j < nw) {
-            uint32_t in = j == 0 ? w0 : __ldg(src + (size_t)j * 32);
-            if (j == 0) {
-                v = (in ^ (seq[0] << 7)) & ~0x7fu; /* outputs 0..6 are forced to 0 (decode_impl.cc:315) */
-            } else {
-                int o = (32 * j - 7) % 127;
-                uint32_t s = __funnelshift_r(seq[o >> 5], seq[(o >> 5) + 1], o & 31);
-                v = in ^ s;
-            }
-            int rem = T - 32 * j; /* bits past the trellis are not data */
-            if (rem < 32) v &= (1u << rem) - 1u;
+        if (lane == 0) {
+            S.src[wid] = src;
+            S.T[wid] = T;
         }
-        dw[j] = v;
+    } else if (lane == 0) {
+        S.src[wid] = bits;
+        S.T[wid] = 0;
     }
-    __syncwarp();
+    __syncthreads();
+    /* The traceback leaves word j of the 32 packets of a group side by side (bits[j][32]); the block's eight packets are
+     * eight neighbours there, so the block reads the words together -- a warp takes four rows of eight packets, four whole
+     * sectors -- descrambles them on the way and lays them out per packet in shared memory (row stride = 4 mod 32 banks:
+     * the transposing store is conflict-free). */
+    {
+        const int pp = tid & (POST_WARPS - 1), jr = tid / POST_WARPS;
+        const int Tp = S.T[pp];
+        const int nwp = Tp > 0 ? (Tp + 31) >> 5 : -1;
+        const uint32_t* srcp = S.src[pp];
+        const uint32_t* seq = S.seq[pp];
+        uint32_t* dwp = S.dw[pp];
+        for (int j = jr; j < nwp + 1; j += 32) { /* blockDim.x / POST_WARPS rows per pass */
+            uint32_t v = 0;
+            if (j < nwp) {
+                const uint32_t in = __ldg(srcp + (size_t)j * 32);
+                if (j == 0) {
+                    v = (in ^ (seq[0] << 7)) & ~0x7fu; /* outputs 0..6 are forced to 0 (decode_impl.cc:315) */
+                } else {
+                    const int o = (32 * j - 7) % 127;
+                    const uint32_t sq = __funnelshift_r(seq[o >> 5], seq[(o >> 5) + 1], o & 31);
+                    v = in ^ sq;
+                }
+                const int rem = Tp - 32 * j; /* bits past the trellis are not data */
+                if (rem < 32) v &= (1u << rem) - 1u;
+            }
+            dwp[j] = v;
+        }
+    }
+    __syncthreads();
+    if (!valid) return;
+    const uint32_t* dw = S.dw[wid];
 
     /* PSDU bytes: byte k = bits 16+8k .. 23+8k */
     const uint8_t* by = reinterpret_cast<const uint8_t*>(dw) + 2;
