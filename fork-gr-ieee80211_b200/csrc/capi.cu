@@ -67,6 +67,7 @@ enum { EV_START, EV_COPIED, EV_H2D, EV_HDR0, EV_HDR, EV_HDRD, EV_PLAN, EV_DEMOD,
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[EV_COUNT] = {};
+    int max_ncbps = 0; /* largest symbol of the batch, in LLRs: sizes the demod kernel's staging rows */
     bool busy = false;
     /* rx_submit returns once the input copies and the header kernel are enqueued; the rest of the batch (host plan, demod,
      * decode) is enqueued by a later API call, when the descriptors have arrived (run_continuation) */
@@ -291,12 +292,14 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     dec.clear();
     key.assign((size_t)npkt, 0);
     s.trellis_steps = 0;
+    s.max_ncbps = 0;
     bool sorted = true;
     uint32_t last_key = 0;
     for (int p = 0; p < npkt; p++) {
         w80211_desc& d = hd[p];
         int nsym = 0;
         if (d.status == W80211_ST_OK && d.total > 0) {
+            s.max_ncbps = std::max(s.max_ncbps, d.ncbps);
             if (assign_llr) {
                 d.llr_off = (int64_t)off;
                 off += align_up((size_t)d.total, 4) + 16;
@@ -621,7 +624,7 @@ int continue_front(w80211_ctx* ctx, Slot& s)
     if (ctx->last_tail && ctx->last_tail != s.ev[EV_POST]) CK(cudaStreamWaitEvent(st, ctx->last_tail, 0));
     CK(cudaEventRecord(s.ev[EV_PLAN], st));
     w_launch_demod(st, ctx->d_tab, s.nsymtot, npkt, s.nant, d_iq[0], d_iq[1], d_pk, (const w80211_desc*)s.desc.p,
-                   (const int*)s.symprefix.p, (const float2*)s.chan.p, chan_stride, (float*)s.llr.p);
+                   (const int*)s.symprefix.p, (const float2*)s.chan.p, chan_stride, (float*)s.llr.p, s.max_ncbps);
     CK(cudaGetLastError());
     if (s.nsymtot) s.launches += 1;
     CK(cudaEventRecord(s.ev[EV_DEMOD], st));

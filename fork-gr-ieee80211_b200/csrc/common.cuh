@@ -192,7 +192,7 @@ void w_launch_header(cudaStream_t st, const W80211Tables* tab, int npkt, int nan
 int w_demod_init_device(); /* per-device kernel attributes, called by w80211_create() with the context's device current */
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nsymtot, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* sym_prefix,
-                    const float2* chan, int chan_stride, float* llr);
+                    const float2* chan, int chan_stride, float* llr, int max_ncbps);
 /* signal stage: per-flag L-SIG result and the copy list of accepted packets */
 struct w_sig_acc {
     unsigned long long src; /* sync position in the raw stream */

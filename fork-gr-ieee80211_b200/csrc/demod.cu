@@ -16,20 +16,25 @@
  * copy-out, and the next symbol's FFT and equalisation run while the row drains.
  */
 #include "common.cuh"
+#include <atomic>
 
-#define DEMOD_THREADS 64
+#define DEMOD_THREADS 64   /* one antenna: 8 groups per block, 8 blocks per SM */
+#ifndef DEMOD_THREADS2
+#define DEMOD_THREADS2 128 /* two antennas: 16 groups per block, 2 blocks per SM (why: at DemodSmem) */
+#endif
 #ifndef DEMOD_MINBLK
 #define DEMOD_MINBLK 8
 #endif
 #ifndef DEMOD_MINBLK2
-#define DEMOD_MINBLK2 4 /* two-antenna variant */
+#define DEMOD_MINBLK2 2 /* two-antenna variant */
 #endif
-#define DEMOD_GROUPS (DEMOD_THREADS / 8)
+template <bool MIMO> struct DemodCfg { enum { THREADS = MIMO ? DEMOD_THREADS2 : DEMOD_THREADS, GROUPS = THREADS / 8 }; };
 #define DEMOD_SPC W_DEMOD_SPC /* most symbols per work item (one 8-lane group walks them in order) */
 #define DEMOD_STAGE 832    /* floats: largest nCBPS (2 streams of 256-QAM) */
-#define DEMOD_PAD 4        /* floats after a group's staging row: rows start 4 banks apart (the deinterleaved positions of the
-                              8 bins a group writes at a time fall on 8 banks that repeat every row of 416 / 832 floats) and
-                              stay 16-byte aligned for the copy-out; the pad is the slot that bins without data write to */
+#define DEMOD_PAD 4        /* floats after a group's staging row: the slot that bins without data write to.  Rows are as long as the
+                              batch's largest symbol (demod_row_floats): an odd number of 16-byte units, so they stay 16-byte aligned
+                              for the copy-out and start an odd multiple of 4 banks apart (the deinterleaved positions of the 8 bins
+                              a group writes at a time fall on 8 banks that repeat from row to row) */
 #define DEMOD_MAPPAD 8     /* map entries after a table, all pointing at that slot */
 
 /* item -> packet: prefix[p] <= w < prefix[p+1].  Batches are mostly homogeneous, so an
@@ -182,15 +187,29 @@ __device__ __forceinline__ void fft64_regs(const float2* v, int g, float2* xch, 
 /* dynamic shared memory of one block (the two-antenna variant needs more than the 48 KB static limit) */
 template <bool MIMO>
 struct DemodSmem {
-    double eqr[MIMO ? 1 : DEMOD_GROUPS][MIMO ? 1 : 64];            /* per bin: RN(1 / |H|^2) in binary64.  Not kept by the two-antenna
-                                                                      variant (its one-stream packets recompute it): at 31.9 KB
-                                                                      per block four blocks leave the SM 32 KB more L1 */
-    alignas(16) float stage[DEMOD_GROUPS][(MIMO ? DEMOD_STAGE : DEMOD_STAGE / 2) + DEMOD_PAD]; /* one symbol's LLRs per group, deinterleaved: the
-                                                                      source of the bulk store; the pad holds the dump slot */
-    alignas(16) float2 xch[DEMOD_GROUPS][W_FFT_XCH_FLOAT2];                    /* FFT exchange area of the group (the staging row may still be
-                                                                      draining when the next symbol's FFT runs) */
-    float2 tw[8 * 9];                                              /* W64^(g*k1) at [g*9 + k1] */
+    enum { GROUPS = DemodCfg<MIMO>::GROUPS };
+    double eqr[MIMO ? 1 : GROUPS][MIMO ? 1 : 64]; /* per bin: RN(1 / |H|^2) in binary64.  Not kept by the two-antenna variant (its
+                                                     one-stream packets recompute it) */
+    alignas(16) float2 xch[GROUPS][W_FFT_XCH_FLOAT2]; /* FFT exchange area of the group (the staging row may still be draining when
+                                                         the next symbol's FFT runs) */
+    float2 tw[8 * 9];                                 /* W64^(g*k1) at [g*9 + k1] */
+    alignas(16) float stage[4];                       /* GROUPS rows of row_floats floats follow: one symbol's LLRs per group,
+                                                         deinterleaved, the source of the bulk store */
 };
+/* Shared memory decides how much L1 the SM keeps (the carve-out is the smallest step that holds the resident blocks), and the
+ * two-antenna variant lives on L1 (channel matrices, table rows: profiles/experiments/r2_demod.txt), so the rows are sized by
+ * the batch, not by the largest symbol of the standard: two blocks of 16 groups of C5 (nCBPS 624) fit the 100 KB step, which
+ * four blocks of 8 groups miss by the second kilobyte the driver reserves per block. */
+__host__ __device__ inline int demod_row_floats(int max_ncbps)
+{
+    int r = ((max_ncbps + 3) & ~3) + DEMOD_PAD;
+    if (((r >> 2) & 1) == 0) r += 4;
+    return r;
+}
+template <bool MIMO> static size_t demod_smem_bytes(int max_ncbps)
+{
+    return offsetof(DemodSmem<MIMO>, stage) + (size_t)DemodCfg<MIMO>::GROUPS * demod_row_floats(max_ncbps) * sizeof(float);
+}
 static_assert(offsetof(W80211Tables, binmap) % 16 == 0, "binmap rows are read as uint4");
 
 /* shared -> global bulk copy by the SM's copy engine, tracked by this thread's bulk async-group (PTX cp.async.bulk) */
@@ -204,7 +223,7 @@ __device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, uint32_
 __device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
 template <bool MIMO> /* MIMO = false: one antenna, no two-stream code or registers at all */
-__global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MINBLK) demod_kernel(const W80211Tables* __restrict__ T, int nitems, int npkt, int nant,
+__global__ void __launch_bounds__(DemodCfg<MIMO>::THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MINBLK) demod_kernel(const W80211Tables* __restrict__ T, int nitems, int npkt, int nant, int row_floats,
                                                               const float2* __restrict__ iq0, const float2* __restrict__ iq1,
                                                               const w80211_pkt_in* __restrict__ pkin,
                                                               const w80211_desc* __restrict__ desc, const int* __restrict__ item_prefix,
@@ -212,13 +231,12 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MI
 {
     extern __shared__ __align__(16) unsigned char demod_smem_raw[];
     DemodSmem<MIMO>& S = *reinterpret_cast<DemodSmem<MIMO>*>(demod_smem_raw);
-    auto& stage = S.stage;
     auto& eqr = S.eqr;
     const int tid = threadIdx.x;
     const int lane = tid & 31, g = tid & 7, base = lane & ~7, grp = tid >> 3;
-    const int w = blockIdx.x * DEMOD_GROUPS + grp;
+    const int w = blockIdx.x * DemodCfg<MIMO>::GROUPS + grp;
     const bool valid = w < nitems;
-    S.tw[(tid >> 3) * 9 + (tid & 7)] = make_float2(C8_W64_RE[((tid >> 3) * (tid & 7)) & 63], C8_W64_IM[((tid >> 3) * (tid & 7)) & 63]);
+    if (tid < 64) S.tw[(tid >> 3) * 9 + (tid & 7)] = make_float2(C8_W64_RE[((tid >> 3) * (tid & 7)) & 63], C8_W64_IM[((tid >> 3) * (tid & 7)) & 63]);
     __syncthreads();
     const float2* tw = S.tw;
 
@@ -249,7 +267,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MI
     const bool two = MIMO && valid && nss == 2;
     const bool any2 = MIMO && __any_sync(0xffffffffu, two);
     const int nloop = __reduce_max_sync(0xffffffffu, nsy);
-    float* stg = stage[grp];
+    float* stg = S.stage + (size_t)grp * row_floats;
     float2* myx = S.xch[grp];
 
     /* per-item constants: channel of the lane's eight bins (one stream), tables, pilot patterns */
@@ -417,20 +435,51 @@ __global__ void __launch_bounds__(DEMOD_THREADS, MIMO ? DEMOD_MINBLK2 : DEMOD_MI
 /* Function attributes are per device: w80211_create() calls this once for the context's device (the current one). */
 int w_demod_init_device()
 {
-    cudaError_t e = cudaFuncSetAttribute(demod_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<true>));
+    cudaError_t e = cudaFuncSetAttribute(demod_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)demod_smem_bytes<true>(DEMOD_STAGE));
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(demod_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DemodSmem<false>));
+        e = cudaFuncSetAttribute(demod_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)demod_smem_bytes<false>(DEMOD_STAGE / 2));
     return e == cudaSuccess ? 0 : -1;
 }
 
+/* Ask for the smallest shared-memory step that holds `blocks` resident blocks (the rest of the 256 KB stays L1); left alone
+ * the driver takes the 132 KB step for two 50 KB blocks that fit the 100 KB one.  The attribute belongs to the function on a
+ * device: it is set again only when the batch's shape changes the answer (two host threads with different shapes may
+ * overwrite each other's choice -- that costs L1, never correctness). */
+template <bool MIMO> static void demod_prefer_carveout(size_t smem_per_block, int blocks)
+{
+    static std::atomic<int> last[64];
+    const size_t need = (smem_per_block + 1024) * (size_t)blocks; /* the driver reserves 1 KB per block */
+    static const int steps_kb[] = {8, 16, 32, 64, 100, 132, 164, 196, 228};
+    int kb = 228;
+    for (int c : steps_kb)
+        if ((size_t)c * 1024 >= need) {
+            kb = c;
+            break;
+        }
+    const int pct = kb * 100 / 228; /* rounded down: the driver rounds the hint up to the next step */
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (last[dev & 63].exchange(pct + 1) == pct + 1) return;
+    cudaFuncSetAttribute(demod_kernel<MIMO>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+}
+
+/* max_ncbps: the largest nCBPS among the batch's packets (sizes the staging rows; anything from 48 to 832) */
 void w_launch_demod(cudaStream_t st, const W80211Tables* tab, int nitems, int npkt, int nant, const float2* iq0,
                     const float2* iq1, const w80211_pkt_in* pk, const w80211_desc* desc, const int* item_prefix,
-                    const float2* chan, int chan_stride, float* llr)
+                    const float2* chan, int chan_stride, float* llr, int max_ncbps)
 {
     if (nitems <= 0) return;
-    int blocks = (nitems + DEMOD_GROUPS - 1) / DEMOD_GROUPS;
-    if (nant == 2)
-        demod_kernel<true><<<blocks, DEMOD_THREADS, sizeof(DemodSmem<true>), st>>>(tab, nitems, npkt, nant, iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
-    else
-        demod_kernel<false><<<blocks, DEMOD_THREADS, sizeof(DemodSmem<false>), st>>>(tab, nitems, npkt, nant, iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
+    if (nant == 2) {
+        max_ncbps = max_ncbps < 48 ? 48 : (max_ncbps > DEMOD_STAGE ? DEMOD_STAGE : max_ncbps);
+        const int G = DemodCfg<true>::GROUPS;
+        demod_prefer_carveout<true>(demod_smem_bytes<true>(max_ncbps), DEMOD_MINBLK2);
+        demod_kernel<true><<<(nitems + G - 1) / G, DemodCfg<true>::THREADS, demod_smem_bytes<true>(max_ncbps), st>>>(
+            tab, nitems, npkt, nant, demod_row_floats(max_ncbps), iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
+    } else {
+        max_ncbps = max_ncbps < 48 ? 48 : (max_ncbps > DEMOD_STAGE / 2 ? DEMOD_STAGE / 2 : max_ncbps);
+        const int G = DemodCfg<false>::GROUPS;
+        demod_prefer_carveout<false>(demod_smem_bytes<false>(max_ncbps), DEMOD_MINBLK);
+        demod_kernel<false><<<(nitems + G - 1) / G, DemodCfg<false>::THREADS, demod_smem_bytes<false>(max_ncbps), st>>>(
+            tab, nitems, npkt, nant, demod_row_floats(max_ncbps), iq0, iq1, pk, desc, item_prefix, chan, chan_stride, llr);
+    }
 }
