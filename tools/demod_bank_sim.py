@@ -5,10 +5,12 @@ import ctypes as C, numpy as np, sys, itertools
 sys.path.insert(0, __import__('os').path.dirname(__import__('os').path.dirname(__import__('os').path.abspath(__file__))))
 import w80211rx
 host=w80211rx.host
+# the leading fields of W80211Tables (csrc/common.cuh); the tables after `map` are not needed here
 TAB_DTYPE = np.dtype([("pilot_p", "<f4", 128), ("ltf_nl", "<f4", 64), ("sig_demap", "i1", 64), ("bin_j_l", "i1", 64),
                       ("bin_j_nl", "i1", 64), ("sigb_deint", "u1", 52), ("sigb_int", "u1", 52),
-                      ("map", "<u2", (19, 416)), ("crc_tab", "<u4", (4, 256)), ("crc_x2n", "<u4", 32), ("crc_xpow8", "<u4", 4224)], align=True)
-L=host.load(); t=np.zeros(1,TAB_DTYPE); L.w80211_fill_tables.argtypes=[C.c_void_p]; L.w80211_fill_tables(t.ctypes.data); t=t[0]
+                      ("map", "<u2", (19, 416))], align=True)
+L=host.load(); raw=np.zeros(1<<20,np.uint8); L.w80211_fill_tables.argtypes=[C.c_void_p]; L.w80211_fill_tables(raw.ctypes.data)
+t=raw[:TAB_DTYPE.itemsize].view(TAB_DTYPE)[0]
 cases={"vht256":(8,8,False),"ht64":(7,6,False),"ht16":(6,4,False),"htqpsk":(5,2,False),"l64":(3,6,True),"l16":(2,4,True)}
 def sim(tabid, nb, legacy, base, xor):
     m=t["map"][tabid].astype(int); binj=(t["bin_j_l"] if legacy else t["bin_j_nl"]).astype(int)
@@ -26,7 +28,7 @@ def sim(tabid, nb, legacy, base, xor):
                 tot+=max(len(v) for v in banks.values()); n+=1
     return tot/n
 if __name__=="__main__":
-    print("current 418 stride:", {k:round(sim(v[0],v[1],v[2],[g*418 for g in range(4)],[0]*4),2) for k,v in cases.items()})
+    print("current 420 stride (nCBPS 416 + 4):", {k:round(sim(v[0],v[1],v[2],[g*420 for g in range(4)],[0]*4),2) for k,v in cases.items()})
     print("old 416 stride:", {k:round(sim(v[0],v[1],v[2],[g*416 for g in range(4)],[0]*4),2) for k,v in cases.items()})
     if "--search" not in sys.argv:
         sys.exit(0)
