@@ -308,8 +308,8 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
         } else if (assign_llr) {
             d.llr_off = -1;
         }
-        /* demod work items: runs of at most spc symbols of one packet.  Two-stream packets take short runs, so that the eight
-         * groups of a block mostly work on one packet and share its 4 KB of channel matrices in L1 */
+        /* demod work items: runs of at most spc symbols of one packet.  Two-stream packets take short runs, so that the 32
+         * groups resident on an SM work on a few packets and share their channel matrices (4 KB each) in L1 */
         const int spc = (s.nant == 2 && d.nss == 2) ? spc2 : W_DEMOD_SPC;
         symprefix[p + 1] = symprefix[p] + (nsym + spc - 1) / spc;
         if (!do_decode || d.status != W80211_ST_OK) continue;
