@@ -439,6 +439,13 @@ def main_gpu(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    lws = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    ndev = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if 1 < lws < ndev and ndev % lws == 0 and os.environ.get("W80211_BENCH_PACK_GPUS") != "1":
+        # fewer ranks than GPUs on the box: spread them over the GPUs (0, 2, 4, 6 of eight) rather than packing them on the first
+        # ones -- the host-fed leg is bound by the PCIe domains the GPUs hang off (profiles/r1_host_feed_8gpu.txt: GPUs 0-3 share
+        # 93 GB/s, GPUs 4-7 141 GB/s), and the resident leg does not care
+        local = local * (ndev // lws)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
@@ -566,7 +573,8 @@ def main_gpu(args):
         "config": {"workload": CONFIGS[CONFIG]["workload"] if MPDU_LEN == 4088 else "PROFILING VARIANT, MPDU %d B, not the benchmark workload" % MPDU_LEN},
         "run": {"packets_per_step_per_gpu": P, "unique_packets": N_UNIQUE, "slots_in_flight": 2,
                 "l2": "inputs larger than L2 (%.1f GB of IQ per step)" % (P * wl.nsamp * 8 * wl.nant / 1e9),
-                "parallelism": "packets sharded by rank, no collective"},
+                "parallelism": "packets sharded by rank, no collective",
+                "gpus": "rank r on GPU r * %d (%d ranks spread over the box's %d GPUs)" % (ndev // lws, lws, ndev) if 1 < lws < ndev and ndev % lws == 0 and os.environ.get("W80211_BENCH_PACK_GPUS") != "1" else "rank r on GPU r"},
         "packets_per_s": npk_ok / (ms * 1e-3), "fcs_ok_per_step": npk_ok / K / world,
         "e2e": e2e_obj(e2e32_bits, e2e32_ms, "fc32", "fc32 (gr_complex), the item type of the reference's block API; pinned host buffers through "
                        "w80211_rx_submit/collect, PCIe-bound: 70.4 KB of samples per 4088-byte MPDU"),
