@@ -63,6 +63,22 @@ def test_mimo_flat_channel_and_siso_packets_on_two_antennas(refgr, rx):
     assert len(msgs) == 10
 
 
+def test_two_antenna_batch_of_every_symbol_size(refgr, rx):
+    """Two-stream packets from BPSK (104 LLRs per symbol) to 256-QAM (832), one-stream packets between them, lengths from
+    two symbols to hundreds, in one batch: the demod kernel's staging rows are as long as the batch's largest symbol and a
+    block's 16 groups straddle packets of every size."""
+    h = np.array([[0.9, 0.3 + 0.25j], [-0.2 + 0.3j, 1.0 - 0.1j]])
+    bs = []
+    for i, (fmt, mcs, nss, ln) in enumerate([(g.F_HT, 8, 2, 40), (g.F_VHT, 8, 2, 1500), (g.F_HT, 11, 2, 333), (g.F_VHT, 0, 2, 90),
+                                             (g.F_HT, 15, 2, 2000), (g.F_VHT, 4, 1, 120), (g.F_L, 0, 1, 60), (g.F_VHT, 7, 2, 64)]):
+        bs.append(gp.gen_batch(fmt, mcs, nss, ln, 3, snr_db=36, seed=700 + i, nrx=2, chan=h[:, :nss]))
+    res, msgs = compare_with_reference(refgr, rx, bs)
+    assert len(msgs) == 24
+    # the same packets in the opposite order (the largest symbol no longer first among the two-stream packets)
+    res, msgs = compare_with_reference(refgr, rx, bs[::-1])
+    assert len(msgs) == 24
+
+
 def test_drop_gates_and_bad_fcs(refgr, rx):
     """Corrupted SIG, L-SIG duration too short, wrong FCS: the same packets reach the demod loop and the
     same (none) are published; good packets around them are unaffected."""
