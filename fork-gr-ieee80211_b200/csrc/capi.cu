@@ -68,6 +68,7 @@ struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[EV_COUNT] = {};
     int max_ncbps = 0; /* largest symbol of the batch, in LLRs: sizes the demod kernel's staging rows */
+    bool surv_is_shared = false; /* this batch's survivors are in ctx->surv_shared (large batch), not in surv */
     bool busy = false;
     /* rx_submit returns once the input copies and the header kernel are enqueued; the rest of the batch (host plan, demod,
      * decode) is enqueued by a later API call, when the descriptors have arrived (run_continuation) */
@@ -131,6 +132,13 @@ struct w80211_ctx {
      * would receive its last byte at about the same time. */
     cudaStream_t cstream = nullptr;
     cudaEvent_t last_tail = nullptr; /* EV_POST of the batch whose decode was enqueued last (see enqueue_front) */
+    /* Survivors live from a batch's Viterbi kernel to its traceback, and large batches run those one after the other whatever
+     * slot they are in (a Viterbi kernel fills the GPU), so from W80211_SURV_SHARE_BYTES up (default 1 GiB) all slots use this
+     * one buffer, in turn: 29.8 GB once instead of once per slot at 113 664 C4 packets.  Smaller batches keep a buffer per slot
+     * and may overlap. */
+    DevBuf surv_shared;
+    size_t surv_share_min = (size_t)1 << 30;
+    cudaEvent_t last_shared_tail = nullptr; /* EV_POST of the last batch that used surv_shared */
     W80211Tables* d_tab = nullptr;
     /* LLR buffers this context has handed out as leases come back here when they retire (under g_lease_mu) */
     std::vector<DevBuf> llr_free;
@@ -368,7 +376,10 @@ int plan_and_upload(w80211_ctx* ctx, Slot& s, w80211_desc* hd, bool assign_llr, 
     RS(dev_reserve(ctx, s.symprefix, (size_t)(npkt + 1) * 4));
     if (assign_llr) RS(llr_reserve(ctx, s, (size_t)(s.n_llr + 64) * 4));
     if (do_decode) {
-        RS(dev_reserve(ctx, s.surv, (size_t)row * 32 * 8 + 1024));
+        const size_t surv_bytes = (size_t)row * 32 * 8 + 1024;
+        s.surv_is_shared = ctx->nslots > 1 && surv_bytes >= ctx->surv_share_min;
+        /* growing the shared buffer frees the old one, which waits for every kernel still using it (cudaFree synchronises) */
+        RS(dev_reserve(ctx, s.surv_is_shared ? ctx->surv_shared : s.surv, surv_bytes));
         RS(dev_reserve(ctx, s.bits, (size_t)wrow * 32 * 4 + 1024));
         RS(dev_reserve(ctx, s.bytes, (size_t)boff + 64));
         RS(dev_reserve(ctx, s.slot_pkt, slot_pkt.size() * 4 + 4));
@@ -424,6 +435,10 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
     NvtxRange nvtx_("w80211 enqueue viterbi/traceback/post");
     cudaStream_t st = s.stream;
     w80211_batch_out* out = s.out;
+    uint2* surv = (uint2*)(s.surv_is_shared ? ctx->surv_shared.p : s.surv.p);
+    /* the shared survivor buffer is free once the traceback of the batch that used it last has run (a batch that came in
+     * through rx_submit has waited for that already, before its demod kernel; a decode-only batch has not) */
+    if (s.surv_is_shared && ctx->last_shared_tail && ctx->last_shared_tail != s.ev[EV_TB]) CK(cudaStreamWaitEvent(st, ctx->last_shared_tail, 0));
     CK(cudaEventRecord(s.ev[EV_VIT0], st));
     int warp_mask = 0;
     for (int cr = 0; cr < 4; cr++) {
@@ -431,13 +446,14 @@ int enqueue_decode_tail(w80211_ctx* ctx, Slot& s)
         if (ctx->vit_mode == W80211_CFG_VITERBI_WARP || (ctx->vit_mode == W80211_CFG_VITERBI_AUTO && npk < ctx->warp_max_pkts)) warp_mask |= 1 << cr;
     }
     int nvit = w_launch_viterbi(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
-                                s.llr_src ? s.llr_src : (const float*)s.llr.p, (uint2*)s.surv.p, warp_mask);
+                                s.llr_src ? s.llr_src : (const float*)s.llr.p, surv, warp_mask);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_VIT], st));
     nvit += w_launch_traceback(st, s.cr_first, (const int4*)s.grp.p, (const int*)s.slot_pkt.p, (const w80211_desc*)s.desc.p,
-                               (const uint2*)s.surv.p, (uint32_t*)s.bits.p, warp_mask);
+                               surv, (uint32_t*)s.bits.p, warp_mask);
     CK(cudaGetLastError());
     CK(cudaEventRecord(s.ev[EV_TB], st));
+    if (s.surv_is_shared) ctx->last_shared_tail = s.ev[EV_TB];
     /* MPDU records: one per packet is the rule, a VHT A-MPDU has one per delimiter walked (up to trellis / 32 + 1).  The
      * buffers start at 1.5 per packet; a batch that produces more is finished by collect_slot(), which knows the exact
      * count by then, grows the buffers and runs the post kernel once more (launch_post_again). */
@@ -852,6 +868,7 @@ int w80211_create(const w80211_cfg* cfg, w80211_ctx** outp)
     ctx->vit_mode = cfg ? (cfg->flags & W80211_CFG_VITERBI_MASK) : W80211_CFG_VITERBI_AUTO;
     if (const char* e = getenv("W80211_WARP_MAX_PKTS")) ctx->warp_max_pkts = atoi(e);
     if (const char* e = getenv("W80211_LEASE_BYTES")) ctx->lease_bytes = (size_t)strtoull(e, nullptr, 10);
+    if (const char* e = getenv("W80211_SURV_SHARE_BYTES")) ctx->surv_share_min = (size_t)strtoull(e, nullptr, 10); /* 0: always shared */
     if (ctx->device < 0 || ctx->device >= ndev || cudaSetDevice(ctx->device) != cudaSuccess) {
         delete ctx;
         return W80211_E_ARG;
@@ -930,6 +947,7 @@ void w80211_destroy(w80211_ctx* ctx)
     if (ctx->cstream) cudaStreamDestroy(ctx->cstream);
     if (ctx->origin) cudaEventDestroy(ctx->origin);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
+    if (ctx->surv_shared.p) cudaFree(ctx->surv_shared.p);
     delete ctx;
 }
 
