@@ -335,6 +335,53 @@ def test_slots_in_flight_equal_one_batch_at_a_time():
         rx4.close()
 
 
+def test_one_survivor_buffer_for_all_slots(monkeypatch):
+    """Large batches keep their survivors in one buffer of the context, used by the slots in turn (W80211_SURV_SHARE_BYTES,
+    default 1 GiB; 0 here, so that small batches take that path too): batches in flight through rx_submit, and decode-only
+    batches in flight through decode_submit (which nothing else orders), some longer than others so that the buffer grows
+    while an earlier batch is still using it.  Results equal one batch at a time on a context that does not share."""
+    batches = [gp.gen_batch(g.F_L, 7, 1, 300, 6, snr_db=30, seed=270), gp.gen_batch(g.F_VHT, 8, 1, 3000, 40, snr_db=30, seed=271),
+               gp.gen_batch(g.F_HT, 7, 1, 1200, 5, snr_db=30, short_gi=True, seed=272), gp.gen_batch(g.F_HT, 15, 2, 4095, 36, snr_db=35, seed=273),
+               gp.gen_batch(g.F_L, 0, 1, 94, 3, snr_db=20, seed=274), gp.gen_batch(g.F_VHT, 3, 1, 900, 70, snr_db=30, seed=275)]
+    packed = [host.pack_batch([b]) for b in batches]
+    plain = host.Receiver(0, nslots=2)
+    try:
+        alone = [plain.rx(*p, want_llr=True) for p in packed]
+    finally:
+        plain.close()
+    monkeypatch.setenv("W80211_SURV_SHARE_BYTES", "0")
+    rx3 = host.Receiver(0, nslots=3)
+    try:
+        for rounds in range(2):
+            got, pend = [None] * len(packed), []
+            for i, p in enumerate(packed):
+                if len(pend) == 3:
+                    j = pend.pop(0)
+                    got[j] = rx3.collect(j % 3)
+                rx3.submit(i % 3, *p)
+                pend.append(i)
+            for j in pend:
+                got[j] = rx3.collect(j % 3)
+            for a, b2, bt in zip(alone, got, batches):
+                assert b2.messages() == a.messages() and len(a.messages()) == len(bt["mpdu"])
+        # decode-only batches, three in flight, LLRs from the host
+        for rounds in range(2):
+            got, pend = [None] * len(packed), []
+            for i, a in enumerate(alone):
+                if len(pend) == 3:
+                    j = pend.pop(0)
+                    got[j] = rx3.collect(j % 3)
+                rx3.decode_submit(i % 3, a.desc, llr=a.llr[: a.n_llr])
+                pend.append(i)
+            for j in pend:
+                got[j] = rx3.collect(j % 3)
+            for a, r in zip(alone, got):
+                r.desc = a.desc
+                assert r.messages() == a.messages()
+    finally:
+        rx3.close()
+
+
 def test_submit_collect_errors_leave_the_slot_usable():
     rx2 = host.Receiver(0, nslots=2)
     try:
