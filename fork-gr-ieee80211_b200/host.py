@@ -134,6 +134,10 @@ def load():
         L.w80211_create.argtypes = [C.POINTER(Cfg), C.POINTER(vp)]
         L.w80211_destroy.argtypes = [vp]
         L.w80211_destroy.restype = None
+        L.w80211_host_alloc.argtypes = [C.c_size_t]
+        L.w80211_host_alloc.restype = vp
+        L.w80211_host_free.argtypes = [vp]
+        L.w80211_host_free.restype = None
         L.w80211_last_error.argtypes = [vp]
         L.w80211_last_error.restype = C.c_char_p
         L.w80211_stats_get.argtypes = [vp, C.POINTER(Stats)]
@@ -246,11 +250,15 @@ class Receiver:
         if r != 0:
             raise W80211Error("w80211_create failed (%d): no usable CUDA device; this library has no CPU path" % r)
         self._keep = {}
+        self._pinned = []  # page-locked result buffers handed out by pinned_zeros()
 
     def close(self):
         if self.h:
             self.L.w80211_destroy(self.h)
             self.h = C.c_void_p()
+        for p in getattr(self, "_pinned", []):
+            self.L.w80211_host_free(p)
+        self._pinned = []
 
     def __del__(self):
         try:
@@ -294,15 +302,28 @@ class Receiver:
         bi.mu_pos = int(mu_pos)
         return bi
 
+    def pinned_zeros(self, n, dtype):
+        """n zeroed elements in page-locked host memory (w80211_host_alloc), freed by close().  With pageable result buffers
+        the device -> host copies at the end of a batch make submit() wait for the whole batch; with these it returns at once."""
+        dtype = np.dtype(dtype)
+        nbytes = max(int(n) * dtype.itemsize, 16)
+        p = self.L.w80211_host_alloc(nbytes)
+        if not p:
+            raise MemoryError("w80211_host_alloc(%d)" % nbytes)
+        self._pinned.append(p)
+        a = np.frombuffer((C.c_char * nbytes).from_address(p), dtype=np.uint8)[: int(n) * dtype.itemsize].view(dtype)
+        a[...] = np.zeros((), dtype)
+        return a
+
     @staticmethod
-    def make_out_host(npkt, bytes_cap, mpdu_cap, llr_cap=0):
+    def make_out_host(npkt, bytes_cap, mpdu_cap, llr_cap=0, zeros=np.zeros):
         bo = BatchOut()
         arrs = {
-            "desc": np.zeros(npkt, DESC_DTYPE),
-            "bytes": np.zeros(max(bytes_cap, 16), np.uint8),
-            "psdu_off": np.zeros(max(npkt, 1), np.uint32),
-            "mpdus": np.zeros(max(mpdu_cap, 1), MPDU_DTYPE),
-            "llr": np.zeros(max(llr_cap, 4), np.float32) if llr_cap else None,
+            "desc": zeros(npkt, DESC_DTYPE),
+            "bytes": zeros(max(bytes_cap, 16), np.uint8),
+            "psdu_off": zeros(max(npkt, 1), np.uint32),
+            "mpdus": zeros(max(mpdu_cap, 1), MPDU_DTYPE),
+            "llr": zeros(max(llr_cap, 4), np.float32) if llr_cap else None,
         }
         bo.mem = MEM_HOST
         bo.desc = arrs["desc"].ctypes.data
@@ -394,8 +415,9 @@ class Receiver:
         r = self.L.w80211_llr_query(int(handle), C.byref(dev), C.byref(n))
         return None if r != 0 else (int(dev.value), int(n.value))
 
-    def decode_submit(self, slot, desc, llr=None, lease=0):
-        """Descriptors + LLRs (host array, or a lease handle) -> bytes on slot `slot` without waiting (w80211_decode_submit)."""
+    def decode_submit(self, slot, desc, llr=None, lease=0, pinned=False):
+        """Descriptors + LLRs (host array, or a lease handle) -> bytes on slot `slot` without waiting (w80211_decode_submit).
+        pinned: result buffers in page-locked memory (see pinned_zeros)."""
         desc = np.ascontiguousarray(desc, DESC_DTYPE)
         npkt = len(desc)
         di = DecodeIn()
@@ -406,7 +428,7 @@ class Receiver:
             llr = np.ascontiguousarray(llr, np.float32)
             di.llr_mem, di.llr, di.nllr = MEM_HOST, llr.ctypes.data, llr.size
         bcap = int(np.maximum(desc["trellis"], 0).astype(np.int64).sum()) // 8 + 64 * npkt + 64
-        bo, arrs = self.make_out_host(npkt, bcap, npkt * 2 + bcap // 32 + 64)
+        bo, arrs = self.make_out_host(npkt, bcap, npkt * 2 + bcap // 32 + 64, zeros=self.pinned_zeros if pinned else np.zeros)
         arrs["desc"][:] = desc
         keep = (di, bo, arrs, desc, llr)
         self._check(self.L.w80211_decode_submit(self.h, slot, C.byref(di), C.byref(bo)))

@@ -364,14 +364,16 @@ def test_one_survivor_buffer_for_all_slots(monkeypatch):
                 got[j] = rx3.collect(j % 3)
             for a, b2, bt in zip(alone, got, batches):
                 assert b2.messages() == a.messages() and len(a.messages()) == len(bt["mpdu"])
-        # decode-only batches, three in flight, LLRs from the host
-        for rounds in range(2):
+        # decode-only batches, three in flight, LLRs from the host; page-locked result buffers, so that decode_submit returns
+        # while the batch runs (with pageable ones the result copies make it wait) and a batch really is enqueued behind one
+        # that still uses the buffer -- without the wait for the previous user's traceback every pair here decodes garbage
+        for rounds in range(3):
             got, pend = [None] * len(packed), []
             for i, a in enumerate(alone):
                 if len(pend) == 3:
                     j = pend.pop(0)
                     got[j] = rx3.collect(j % 3)
-                rx3.decode_submit(i % 3, a.desc, llr=a.llr[: a.n_llr])
+                rx3.decode_submit(i % 3, a.desc, llr=a.llr[: a.n_llr], pinned=True)
                 pend.append(i)
             for j in pend:
                 got[j] = rx3.collect(j % 3)
