@@ -353,11 +353,13 @@ class Receiver:
         self._check(self.L.w80211_rx_batch(self.h, C.byref(bi), C.byref(bo)))
         return Result(arrs["desc"], arrs["bytes"], arrs["psdu_off"], arrs["mpdus"], bo, arrs["llr"])
 
-    def submit(self, slot, iq, pkts, chan, want_llr=False, mu_pos=0, bytes_cap=None):
-        """IQ -> bytes on slot `slot` without waiting (w80211_rx_submit); collect(slot) returns the Result."""
+    def submit(self, slot, iq, pkts, chan, want_llr=False, mu_pos=0, bytes_cap=None, pinned=False):
+        """IQ -> bytes on slot `slot` without waiting (w80211_rx_submit); collect(slot) returns the Result.
+        pinned: result buffers in page-locked memory (see pinned_zeros)."""
         bcap, mcap, lcap = self._caps(iq, pkts)
         bi = self.make_in(iq, pkts, chan, mu_pos=mu_pos)
-        bo, arrs = self.make_out_host(len(pkts), bcap if bytes_cap is None else bytes_cap, mcap, lcap if want_llr else 0)
+        bo, arrs = self.make_out_host(len(pkts), bcap if bytes_cap is None else bytes_cap, mcap, lcap if want_llr else 0,
+                                      zeros=self.pinned_zeros if pinned else np.zeros)
         keep = (bi, bo, arrs, iq, pkts, chan)  # the library reads them until collect()
         self._check(self.L.w80211_rx_submit(self.h, slot, C.byref(bi), C.byref(bo)))
         self._keep[slot] = keep

@@ -321,7 +321,7 @@ def test_slots_in_flight_equal_one_batch_at_a_time():
                 if len(pend) == 4:
                     j = pend.pop(0)
                     got[j] = rx4.collect(j % 4)
-                rx4.submit(s, *p, want_llr=True)
+                rx4.submit(s, *p, want_llr=True, pinned=rounds == 1)  # page-locked results: nothing in submit() waits for the GPU
                 pend.append(i)
             for j in pend:
                 got[j] = rx4.collect(j % 4)
@@ -358,7 +358,7 @@ def test_one_survivor_buffer_for_all_slots(monkeypatch):
                 if len(pend) == 3:
                     j = pend.pop(0)
                     got[j] = rx3.collect(j % 3)
-                rx3.submit(i % 3, *p)
+                rx3.submit(i % 3, *p, pinned=True)
                 pend.append(i)
             for j in pend:
                 got[j] = rx3.collect(j % 3)
